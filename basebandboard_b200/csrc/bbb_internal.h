@@ -1,0 +1,77 @@
+// bbb_internal.h -- shared between the translation units of libbbb_b200.so.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/bbb_b200.h"
+
+#define BBB_MAX_N 512
+#define BBB_MAX_NW64 (BBB_MAX_N / 64)
+#define BBB_MAX_NW32 (BBB_MAX_N / 32)
+
+// Dense n x n GF(2) matrix on the host, row-major, 64-bit words, bit c of row r
+// = word c/64 bit c%64.  Used only to precompute jump-ahead operators A^e
+// ("host precomputes A^(2^i) by repeated squaring").
+struct HostMat {
+    uint32_t n = 0, nw = 0;
+    std::vector<uint64_t> w;  // n * nw
+    void init(uint32_t n_) { n = n_; nw = (n_ + 63) / 64; w.assign((size_t)n * nw, 0); }
+    uint64_t *row(uint32_t r) { return &w[(size_t)r * nw]; }
+    const uint64_t *row(uint32_t r) const { return &w[(size_t)r * nw]; }
+    void set_identity();
+    static void mul(HostMat &c, const HostMat &a, const HostMat &b);   // c = a.b
+    void apply(const uint64_t *x, uint64_t *y) const;                  // y = M.x (may alias)
+    // Column-major 32-bit words for the seeding kernel: out[c*nw32 + w].
+    void to_colmajor32(std::vector<uint32_t> &out) const;
+};
+
+struct bbb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 0;
+    std::string err;
+    double last_ms = 0.0;
+    uint32_t last_launches = 0;
+    const char *last_kernel = "none";
+
+    // loaded LUTOPT recurrence
+    uint32_t n = 0;
+    std::vector<uint32_t> row_ptr;
+    std::vector<uint16_t> taps;
+    int shipped = 0;              // n of the shipped matrix this equals, else 0
+    HostMat A;                    // dense A
+    std::vector<HostMat> Apow2;   // A^(2^i), grown on demand
+    uint32_t *d_row_ptr = nullptr;   // device copies for the generic kernel
+    uint16_t *d_taps = nullptr;
+
+    // scratch device buffers (grown on demand)
+    void *d_scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+
+    int fail(int code, const char *fmt, ...);
+    int cuda_fail(cudaError_t e, const char *what);
+    void *scratch(int slot, size_t bytes);   // nullptr on failure (err set)
+    void begin_call();                       // resets timing counters, records ev0
+    void end_call();                         // records ev1 (call bbb_sync before reading ms)
+    const HostMat &pow2(uint32_t i);         // A^(2^i)
+    void power(uint64_t e, HostMat &out);    // A^e
+};
+
+#define BBB_CUDA(ctx, call)                                       \
+    do {                                                          \
+        cudaError_t e__ = (call);                                 \
+        if (e__ != cudaSuccess) return (ctx)->cuda_fail(e__, #call); \
+    } while (0)
+
+// clt.cu
+int bbb_clt_run_device(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                       uint64_t *d_hist /*n+1 u64 or null*/, int8_t *d_out8, int16_t *d_out16,
+                       uint32_t noise_var, uint32_t *d_out_words32);

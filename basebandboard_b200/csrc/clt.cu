@@ -1,0 +1,459 @@
+// clt.cu -- LUTOPT -> CLTGRNG on the device (gateware/bbb/rng.py:21-40, :70-108).
+//
+// Layout of the computation (DESIGN.md "CLT path"):
+//   * the sample range is cut into S independent streams of L = 2^k samples; stream s
+//     starts from A^(s*L) . x_level, obtained on the device from host-precomputed
+//     jump-ahead operators A^(L*2^b) (seed kernel, one warp per 32 streams);
+//   * generators are BIT-SLICED: a thread owns 32 streams, register/shared word i
+//     holds state bit i of all 32 (bit j of the word = stream j of the thread);
+//   * one LUTOPT clock is the sparse XOR network x'[r] = XOR x[taps(r)] on those
+//     words; the CLT tree (rng.py:96-105) equals popcount(x' XOR M) - n/2 with
+//     M = indices of odd bit-parity, computed by a carry-save
+//     adder network on the same words;
+//   * counts are un-sliced with a 32x32 bit transpose and histogrammed / stored.
+//
+// This file holds the seed kernel, the data-driven kernel that works for ANY
+// loaded recurrence ("generic"), and the dispatch; the straight-line kernels
+// generated for the shipped matrices live in clt_spec.cu.
+#include "bbb_internal.h"
+#include "clt_common.cuh"
+
+// ---------------------------------------------------------------------------
+// seed kernel: planes[i*T + t] = bit i of the 32 streams of main-kernel thread t
+// ---------------------------------------------------------------------------
+template <int NW32>
+__global__ void __launch_bounds__(256)
+seed_kernel(const uint32_t *__restrict__ J,   // [nbits][n][NW32] column-major jump operators
+            SeedStart xs, uint32_t n, uint32_t nbits, uint32_t T, uint32_t *__restrict__ planes)
+{
+    const uint32_t gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;   // = main-kernel thread
+    const uint32_t lane = threadIdx.x & 31;
+    if (gw >= T) return;
+    const uint32_t s = gw * 32 + lane;   // stream index
+    uint32_t x[NW32];
+#pragma unroll
+    for (int w = 0; w < NW32; w++) x[w] = xs.w[w];
+    for (uint32_t b = 0; b < nbits; b++) {
+        const bool mine = (s >> b) & 1;
+        if (!__any_sync(0xffffffffu, mine)) continue;   // warp-uniform for b >= 5
+        const uint32_t *Jb = J + (size_t)b * n * NW32;
+        uint32_t acc[NW32];
+#pragma unroll
+        for (int w = 0; w < NW32; w++) acc[w] = 0;
+#pragma unroll
+        for (int xw = 0; xw < NW32; xw++) {
+            const uint32_t word = x[xw];
+            const uint32_t cend = min(32u, n - (uint32_t)xw * 32u);
+            for (uint32_t k = 0; k < cend; k++) {
+                const uint32_t m = 0u - ((word >> k) & 1u);
+                const uint32_t *col = Jb + (size_t)(xw * 32 + k) * NW32;
+#pragma unroll
+                for (int w = 0; w < NW32; w++) acc[w] ^= __ldg(col + w) & m;
+            }
+        }
+        if (mine) {
+#pragma unroll
+            for (int w = 0; w < NW32; w++) x[w] = acc[w];
+        }
+    }
+    // ballot transpose: word i of thread gw = bit i of every lane's state
+    for (uint32_t i0 = 0; i0 < n; i0 += 32) {
+        uint32_t keep = 0;
+        uint32_t xw = 0;
+#pragma unroll
+        for (int w = 0; w < NW32; w++) if ((uint32_t)w == (i0 >> 5)) xw = x[w];
+#pragma unroll
+        for (int k = 0; k < 32; k++) {
+            const uint32_t bal = __ballot_sync(0xffffffffu, (xw >> k) & 1u);
+            if (lane == (uint32_t)k) keep = bal;
+        }
+        if (i0 + lane < n) planes[(size_t)(i0 + lane) * T + gw] = keep;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// generic main kernel: any recurrence, taps read from shared memory
+// ---------------------------------------------------------------------------
+struct GenericParams {
+    uint32_t n, nnz, T, L, model, noise_var, nw32out;
+    uint64_t nvalid;            // streams s < nvalid are real
+    uint64_t out_base;          // sample offset of stream 0 in the output arrays
+    const uint32_t *row_ptr;
+    const uint16_t *taps;
+    const uint32_t *planes;     // [n][T]
+    unsigned long long *hist;   // n+1 bins or null
+    int8_t *out8;
+    int16_t *out16;
+    uint32_t *out_words;        // raw URNG words, nw32out 32-bit words per sample
+    uint32_t want_clt;
+};
+
+__global__ void __launch_bounds__(256)
+clt_generic_kernel(GenericParams p)
+{
+    extern __shared__ uint32_t smem[];
+    const uint32_t B = blockDim.x, tid = threadIdx.x, n = p.n;
+    uint32_t *cur = smem;
+    uint32_t *nxt = smem + (size_t)n * B;
+    uint32_t *sh_hist = nxt + (size_t)n * B;                 // n+1 bins
+    uint16_t *sh_rp = (uint16_t *)(sh_hist + n + 1);         // n+1
+    uint16_t *sh_tp = sh_rp + (n + 1) + ((n + 1) & 1);       // nnz
+
+    for (uint32_t i = tid; i <= n; i += B) { sh_rp[i] = (uint16_t)p.row_ptr[i]; sh_hist[i] = 0; }
+    for (uint32_t i = tid; i < p.nnz; i += B) sh_tp[i] = p.taps[i];
+    const uint32_t t = blockIdx.x * B + tid;                 // main thread index
+    const bool live = t < p.T;
+    for (uint32_t i = 0; i < n; i++) cur[i * B + tid] = live ? p.planes[(size_t)i * p.T + t] : 0u;
+    __syncthreads();
+
+    // which of my 32 streams are real
+    uint32_t vmask = 0;
+    if (live) {
+        const uint64_t s0 = (uint64_t)t * 32;
+        if (s0 + 32 <= p.nvalid) vmask = 0xffffffffu;
+        else if (s0 < p.nvalid) vmask = (1u << (uint32_t)(p.nvalid - s0)) - 1u;
+    }
+    const uint32_t half = n >> 1;
+    // flush the block histogram before a 32-bit bin can overflow
+    const uint32_t flush_every = 0x7fffffffu / (B * 32u);
+    uint32_t since_flush = 0;
+
+    for (uint32_t step = 0; step < p.L; step++) {
+        // ---- one LUTOPT clock: nxt = A . cur (rng.py:38-40) ----
+        for (uint32_t r = 0; r < n; r++) {
+            uint32_t acc = 0;
+            const uint32_t e = sh_rp[r + 1];
+            for (uint32_t j = sh_rp[r]; j < e; j++) acc ^= cur[(uint32_t)sh_tp[j] * B + tid];
+            nxt[r * B + tid] = acc;
+        }
+        { uint32_t *tmp = cur; cur = nxt; nxt = tmp; }
+
+        // ---- raw URNG words (LUTOPT.x each clock, rng.py:27) ----
+        if (p.out_words) {
+            for (uint32_t w = 0; w < p.nw32out; w++) {
+                uint32_t a[32];
+#pragma unroll
+                for (int k = 0; k < 32; k++) {
+                    const uint32_t i = w * 32 + k;
+                    a[k] = i < n ? cur[i * B + tid] : 0u;
+                }
+                transpose32(a);
+#pragma unroll
+                for (int j = 0; j < 32; j++) {
+                    if ((vmask >> j) & 1u) {
+                        const uint64_t smp = p.out_base + ((uint64_t)t * 32 + j) * p.L + step;
+                        p.out_words[smp * p.nw32out + w] = a[j];
+                    }
+                }
+            }
+        }
+
+        if (p.want_clt) {
+            // ---- popcount(x ^ M): carry-save network, 8 planes per round ----
+            uint32_t a1 = 0, a2 = 0, a4 = 0, hi[7] = {0, 0, 0, 0, 0, 0, 0};
+            for (uint32_t i0 = 0; i0 < n; i0 += 8) {
+                uint32_t q[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint32_t i = i0 + k;
+                    // M: inputs of odd index parity enter the tree negated (rng.py:96-105)
+                    q[k] = cur[i * B + tid] ^ (0u - (uint32_t)(__popc(i) & 1));
+                }
+                uint32_t t2a, t2b, t4a, t4b, e8;
+                csa(t2a, a1, a1, q[0], q[1]);
+                csa(t2b, a1, a1, q[2], q[3]);
+                csa(t4a, a2, a2, t2a, t2b);
+                csa(t2a, a1, a1, q[4], q[5]);
+                csa(t2b, a1, a1, q[6], q[7]);
+                csa(t4b, a2, a2, t2a, t2b);
+                csa(e8, a4, a4, t4a, t4b);
+#pragma unroll
+                for (int k = 0; k < 7; k++) {   // ripple the weight-8 carry into bits 3..9
+                    const uint32_t c = hi[k] & e8;
+                    hi[k] ^= e8;
+                    e8 = c;
+                }
+            }
+            uint32_t a[32];
+#pragma unroll
+            for (int k = 0; k < 32; k++) a[k] = 0;
+            a[0] = a1; a[1] = a2; a[2] = a4;
+#pragma unroll
+            for (int k = 0; k < 7; k++) a[3 + k] = hi[k];
+            transpose32(a);   // a[j] = popcount of stream j
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+                if ((vmask >> j) & 1u) {
+                    uint32_t v = a[j];
+                    if (p.model == BBB_MODEL_GATEWARE) v &= (n - 1);   // Signal((logn, True)), rng.py:78
+                    if (p.hist) atomicAdd(&sh_hist[v], 1u);
+                    const int32_t g = (int32_t)v - (int32_t)half;
+                    const uint64_t smp = p.out_base + ((uint64_t)t * 32 + j) * p.L + step;
+                    if (p.out8) p.out8[smp] = (int8_t)g;
+                    if (p.out16) p.out16[smp] = (int16_t)(g * (int32_t)p.noise_var);   // tx.py:75-76
+                }
+            }
+            if (p.hist && ++since_flush >= flush_every) {
+                __syncthreads();
+                for (uint32_t i = tid; i <= n; i += B) {
+                    if (sh_hist[i]) atomicAdd(&p.hist[i], (unsigned long long)sh_hist[i]);
+                    sh_hist[i] = 0;
+                }
+                __syncthreads();
+                since_flush = 0;
+            }
+        }
+    }
+    if (p.hist) {
+        __syncthreads();
+        for (uint32_t i = tid; i <= n; i += B)
+            if (sh_hist[i]) atomicAdd(&p.hist[i], (unsigned long long)sh_hist[i]);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// host side: geometry, seeding, dispatch
+// ---------------------------------------------------------------------------
+static int launch_seed(bbb_ctx *c, const uint32_t *dJ, const SeedStart &xs, uint32_t nbits, uint32_t T,
+                       uint32_t *d_planes)
+{
+    const uint32_t n = c->n, nw32 = (n + 31) / 32;
+    const uint32_t threads = 256;
+    const uint32_t blocks = (uint32_t)(((uint64_t)T * 32 + threads - 1) / threads);
+#define SEED_CASE(NW) \
+    case NW: seed_kernel<NW><<<blocks, threads, 0, c->stream>>>(dJ, xs, n, nbits, T, d_planes); break
+    switch (nw32) {
+        SEED_CASE(1); SEED_CASE(2); SEED_CASE(3); SEED_CASE(4); SEED_CASE(5); SEED_CASE(6); SEED_CASE(7);
+        SEED_CASE(8); SEED_CASE(9); SEED_CASE(10); SEED_CASE(11); SEED_CASE(12); SEED_CASE(13);
+        SEED_CASE(14); SEED_CASE(15); SEED_CASE(16);
+    default: return c->fail(BBB_EINVAL, "n too large");
+    }
+#undef SEED_CASE
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    return BBB_OK;
+}
+
+// clt_spec.cu: returns 1 if a specialised kernel took the level, 0 if none applies, <0 on error
+int bbb_clt_spec_level(bbb_ctx *c, const SpecLevel &lv);
+int bbb_clt_spec_threads_per_sm(const bbb_ctx *c, bool hist_only, uint32_t *block);
+
+int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                       uint64_t *d_hist, int8_t *d_out8, int16_t *d_out16, uint32_t noise_var,
+                       uint32_t *d_out_words32)
+{
+    const uint32_t n = c->n, nw32 = (n + 31) / 32, nw64 = (n + 63) / 64;
+    const bool want_clt = d_hist || d_out8 || d_out16;
+    if (want_clt && (n & (n - 1))) return c->fail(BBB_EINVAL, "CLTGRNG needs n a power of two (rng.py:73-74), n=%u", n);
+    if (d_out8 && n > 256) return c->fail(BBB_EINVAL, "int8 samples need n <= 256");
+    BBB_CUDA(c, cudaSetDevice(c->device));
+
+    // state at `first`
+    uint64_t xl[BBB_MAX_NW64] = {0};
+    memcpy(xl, x0, nw64 * sizeof(uint64_t));
+    if (n % 64) xl[nw64 - 1] &= (1ull << (n % 64)) - 1;
+    for (uint32_t i = 0; i < 64 && (first >> i); i++)
+        if ((first >> i) & 1) c->pow2(i).apply(xl, xl);
+
+    // generic-kernel geometry
+    uint32_t Bg = 256;
+    while (Bg > 32 && (size_t)8 * n * Bg > 200 * 1024) Bg -= 32;
+    const size_t g_smem = (size_t)8 * n * Bg + (n + 1) * 4 + ((n + 2) & ~1u) * 2 + c->taps.size() * 2 + 16;
+
+    const bool hist_only = d_hist && !d_out8 && !d_out16 && !d_out_words32;
+    uint32_t spec_block = 0;
+    const int spec_tps = bbb_clt_spec_threads_per_sm(c, hist_only, &spec_block);
+    const uint32_t tps = spec_tps > 0 ? (uint32_t)spec_tps : Bg;
+    const uint64_t Sres = (uint64_t)c->sm_count * tps * 32;
+    const uint32_t Lmin = 64;
+
+    uint64_t done = 0;
+    c->last_kernel = "generic";
+    while (done < count) {
+        const uint64_t rem = count - done;
+        // L = 2^k steps per stream, S streams (see file header)
+        uint32_t logL = 0;
+        if (rem >= Lmin) {
+            logL = 6;
+            while (logL < 40 && (rem >> logL) > 8 * Sres) logL++;
+        }
+        const uint64_t L = 1ull << logL;
+        const uint64_t S = rem >> logL;                     // >= 1
+        const uint64_t T64 = (S + 31) / 32;
+        if (T64 > 0x7fffffffull / 32) return c->fail(BBB_EINVAL, "range too large");
+        const uint32_t T = (uint32_t)T64;
+        uint32_t nbits = 0;
+        while (nbits < 40 && ((S - 1) >> nbits)) nbits++;
+
+        // jump operators A^(L*2^b), column-major 32-bit words
+        uint32_t *dJ = (uint32_t *)c->scratch(0, (size_t)(nbits ? nbits : 1) * n * nw32 * 4);
+        if (!dJ) return BBB_ECUDA;
+        {
+            std::vector<uint32_t> all((size_t)nbits * n * nw32), one;
+            for (uint32_t b = 0; b < nbits; b++) {
+                c->pow2(logL + b).to_colmajor32(one);
+                memcpy(&all[(size_t)b * n * nw32], one.data(), one.size() * 4);
+            }
+            if (nbits) BBB_CUDA(c, cudaMemcpyAsync(dJ, all.data(), all.size() * 4, cudaMemcpyHostToDevice, c->stream));
+            BBB_CUDA(c, cudaStreamSynchronize(c->stream));   // `all` is pageable host memory
+        }
+        uint32_t *d_planes = (uint32_t *)c->scratch(1, (size_t)n * T * 4);
+        if (!d_planes) return BBB_ECUDA;
+        SeedStart xs;
+        for (uint32_t w = 0; w < BBB_MAX_NW32; w++)
+            xs.w[w] = w < 2 * nw64 ? (uint32_t)(xl[w >> 1] >> (32 * (w & 1))) : 0u;
+        int rc = launch_seed(c, dJ, xs, nbits, T, d_planes);
+        if (rc) return rc;
+
+        SpecLevel lv;
+        lv.T = T; lv.logL = logL; lv.nvalid = S; lv.out_base = done; lv.model = model;
+        lv.noise_var = noise_var; lv.planes = d_planes; lv.hist = (unsigned long long *)d_hist;
+        lv.out8 = d_out8; lv.out16 = d_out16; lv.out_words = d_out_words32;
+        rc = bbb_clt_spec_level(c, lv);
+        if (rc < 0) return rc;
+        if (rc == 0) {
+            GenericParams p;
+            p.n = n; p.nnz = (uint32_t)c->taps.size(); p.T = T; p.L = (uint32_t)L; p.model = model;
+            p.noise_var = noise_var; p.nw32out = 2 * nw64; p.nvalid = S; p.out_base = done;
+            p.row_ptr = c->d_row_ptr; p.taps = c->d_taps; p.planes = d_planes;
+            p.hist = (unsigned long long *)d_hist; p.out8 = d_out8; p.out16 = d_out16;
+            p.out_words = d_out_words32; p.want_clt = want_clt ? 1u : 0u;
+            if (L > 0xffffffffull) return c->fail(BBB_EINVAL, "L too large");
+            BBB_CUDA(c, cudaFuncSetAttribute(clt_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)g_smem));
+            const uint32_t blocks = (T + Bg - 1) / Bg;
+            clt_generic_kernel<<<blocks, Bg, g_smem, c->stream>>>(p);
+            c->last_launches++;
+            BBB_CUDA(c, cudaGetLastError());
+        }
+        // advance the level's start state by S*L clocks
+        const uint64_t adv = S << logL;
+        for (uint32_t i = 0; i < 64 && (adv >> i); i++)
+            if ((adv >> i) & 1) c->pow2(i).apply(xl, xl);
+        done += adv;
+    }
+    return BBB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------
+static int check_loaded(bbb_ctx *c, const uint64_t *x0)
+{
+    if (!c) return BBB_EINVAL;
+    if (!x0) return c->fail(BBB_EINVAL, "x0 is null");
+    if (!c->n) return c->fail(BBB_ESTATE, "no recurrence loaded (bbb_lutopt_load)");
+    return BBB_OK;
+}
+
+extern "C" {
+
+int bbb_clt_hist_dev(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                     uint64_t *acc_dev)
+{
+    int rc = check_loaded(c, x0);
+    if (rc) return rc;
+    if (!acc_dev) return c->fail(BBB_EINVAL, "acc_dev is null");
+    if (model > 1) return c->fail(BBB_EINVAL, "bad model");
+    c->begin_call();
+    // the kernels accumulate into a zeroed scratch histogram; a tiny kernel then folds it and the
+    // moments (exact integer sums over the bins) into acc_dev
+    const uint32_t n = c->n;
+    uint64_t *d_h = (uint64_t *)c->scratch(2, (n + 1) * sizeof(uint64_t));
+    if (!d_h) return BBB_ECUDA;
+    BBB_CUDA(c, cudaMemsetAsync(d_h, 0, (n + 1) * sizeof(uint64_t), c->stream));
+    rc = bbb_clt_run_device(c, x0, first, count, model, d_h, nullptr, nullptr, 1, nullptr);
+    if (rc) return rc;
+    fold_hist_kernel<<<1, 512, 0, c->stream>>>((const unsigned long long *)d_h, n,
+                                                (unsigned long long *)acc_dev);
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    c->end_call();
+    return BBB_OK;
+}
+
+int bbb_clt_hist(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                 uint64_t *hist, int64_t *sum, uint64_t *sumsq)
+{
+    int rc = check_loaded(c, x0);
+    if (rc) return rc;
+    const uint32_t n = c->n;
+    uint64_t *d_acc = (uint64_t *)c->scratch(3, (n + 3) * sizeof(uint64_t));
+    if (!d_acc) return BBB_ECUDA;
+    BBB_CUDA(c, cudaMemsetAsync(d_acc, 0, (n + 3) * sizeof(uint64_t), c->stream));
+    rc = bbb_clt_hist_dev(c, x0, first, count, model, d_acc);
+    if (rc) return rc;
+    uint64_t h[BBB_MAX_N + 3];
+    BBB_CUDA(c, cudaMemcpyAsync(h, d_acc, (n + 3) * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    const uint32_t bins = n + (model == BBB_MODEL_NUMPY ? 1 : 0);
+    if (hist) for (uint32_t b = 0; b < bins; b++) hist[b] += h[b];
+    if (sum) *sum += (int64_t)h[n + 1];
+    if (sumsq) *sumsq += h[n + 2];
+    return BBB_OK;
+}
+
+int bbb_clt_stream_dev(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                       uint32_t noise_var, int8_t *out8_dev, int16_t *out16_dev)
+{
+    int rc = check_loaded(c, x0);
+    if (rc) return rc;
+    if ((out8_dev != nullptr) == (out16_dev != nullptr))
+        return c->fail(BBB_EINVAL, "exactly one of out8/out16 must be given");
+    if (model > 1) return c->fail(BBB_EINVAL, "bad model");
+    if (noise_var > 15 && out16_dev && (uint64_t)noise_var * (c->n / 2) > 32767)
+        return c->fail(BBB_EINVAL, "noise_var too large for int16");
+    c->begin_call();
+    rc = bbb_clt_run_device(c, x0, first, count, model, nullptr, out8_dev, out16_dev, noise_var, nullptr);
+    if (rc) return rc;
+    c->end_call();
+    return BBB_OK;
+}
+
+int bbb_clt_stream(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                   uint32_t noise_var, int8_t *out8, int16_t *out16)
+{
+    int rc = check_loaded(c, x0);
+    if (rc) return rc;
+    if ((out8 != nullptr) == (out16 != nullptr))
+        return c->fail(BBB_EINVAL, "exactly one of out8/out16 must be given");
+    const size_t bytes = (size_t)count * (out8 ? 1 : 2);
+    void *d = c->scratch(4, bytes ? bytes : 1);
+    if (!d) return BBB_ECUDA;
+    rc = bbb_clt_stream_dev(c, x0, first, count, model, noise_var, out8 ? (int8_t *)d : nullptr,
+                            out16 ? (int16_t *)d : nullptr);
+    if (rc) return rc;
+    BBB_CUDA(c, cudaMemcpyAsync(out8 ? (void *)out8 : (void *)out16, d, bytes, cudaMemcpyDeviceToHost, c->stream));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return BBB_OK;
+}
+
+int bbb_lutopt_stream_dev(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count,
+                          uint64_t *out_words_dev)
+{
+    int rc = check_loaded(c, x0);
+    if (rc) return rc;
+    if (!out_words_dev) return c->fail(BBB_EINVAL, "out is null");
+    c->begin_call();
+    rc = bbb_clt_run_device(c, x0, first, count, 0, nullptr, nullptr, nullptr, 1, (uint32_t *)out_words_dev);
+    if (rc) return rc;
+    c->end_call();
+    return BBB_OK;
+}
+
+int bbb_lutopt_stream(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint64_t *out_words)
+{
+    int rc = check_loaded(c, x0);
+    if (rc) return rc;
+    if (!out_words) return c->fail(BBB_EINVAL, "out is null");
+    const size_t bytes = (size_t)count * ((c->n + 63) / 64) * 8;
+    void *d = c->scratch(4, bytes ? bytes : 1);
+    if (!d) return BBB_ECUDA;
+    rc = bbb_lutopt_stream_dev(c, x0, first, count, (uint64_t *)d);
+    if (rc) return rc;
+    BBB_CUDA(c, cudaMemcpyAsync(out_words, d, bytes, cudaMemcpyDeviceToHost, c->stream));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return BBB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,78 @@
+// clt_common.cuh -- device helpers shared by the CLT / LUTOPT kernels.
+#pragma once
+#include <cstdint>
+
+struct SeedStart {
+    uint32_t w[16];   // level start state, 32-bit little-endian words
+};
+
+// One level of the stream decomposition handed to a specialised kernel.
+struct SpecLevel {
+    uint32_t T;            // main-kernel threads (32 streams each)
+    uint32_t logL;         // every stream runs 2^logL clocks
+    uint64_t nvalid;       // streams s < nvalid are real
+    uint64_t out_base;     // sample offset of stream 0 in the output arrays
+    uint32_t model, noise_var;
+    const uint32_t *planes;        // [n][T] bit-sliced start states
+    unsigned long long *hist;      // n+1 bins or null
+    int8_t *out8;
+    int16_t *out16;
+    uint32_t *out_words;
+};
+
+// carry-save adder: (carry, sum) = a + b + c, bitwise over 32 streams (2 LOP3)
+__device__ __forceinline__ void csa(uint32_t &carry, uint32_t &sum, uint32_t a, uint32_t b, uint32_t c)
+{
+    const uint32_t s = a ^ b ^ c;
+    carry = (a & b) | (a & c) | (b & c);
+    sum = s;
+}
+
+// In-place transpose of a 32x32 bit matrix: on return bit k of a[j] is what bit j
+// of a[k] was (LSB = column 0).  5 butterfly stages.
+__device__ __forceinline__ void transpose32(uint32_t (&a)[32])
+{
+#pragma unroll
+    for (int s = 0; s < 5; s++) {
+        const int j = 16 >> s;
+        const uint32_t m = s == 0 ? 0x0000FFFFu : s == 1 ? 0x00FF00FFu : s == 2 ? 0x0F0F0F0Fu
+                          : s == 3 ? 0x33333333u : 0x55555555u;
+#pragma unroll
+        for (int k = 0; k < 32; k++) {
+            if (k & j) continue;
+            const uint32_t t = ((a[k] >> j) ^ a[k + j]) & m;
+            a[k + j] ^= t;
+            a[k] ^= t << j;
+        }
+    }
+}
+
+// acc[0..n] += hist[0..n]; acc[n+1] += sum g*h; acc[n+2] += sum g^2*h with g = bin - n/2.
+// Exact integer arithmetic: the moments of the sample set are functions of its histogram.
+static __global__ void fold_hist_kernel(const unsigned long long *__restrict__ hist, uint32_t n,
+                                 unsigned long long *__restrict__ acc)
+{
+    __shared__ long long s1[512];
+    __shared__ unsigned long long s2[512];
+    const uint32_t tid = threadIdx.x;
+    long long a = 0;
+    unsigned long long b = 0;
+    for (uint32_t i = tid; i <= n; i += blockDim.x) {
+        const unsigned long long h = hist[i];
+        const long long g = (long long)i - (long long)(n / 2);
+        acc[i] += h;
+        a += g * (long long)h;
+        b += (unsigned long long)(g * g) * h;
+    }
+    s1[tid] = a;
+    s2[tid] = b;
+    __syncthreads();
+    for (uint32_t st = blockDim.x / 2; st; st >>= 1) {
+        if (tid < st) { s1[tid] += s1[tid + st]; s2[tid] += s2[tid + st]; }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        acc[n + 1] += (unsigned long long)s1[0];
+        acc[n + 2] += s2[0];
+    }
+}

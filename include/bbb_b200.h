@@ -1,0 +1,187 @@
+/*
+ * bbb_b200.h -- C ABI of the B200-native noise / test-pattern datapath of
+ * adamgreig/basebandboard (libbbb_b200.so, hand-written CUDA for sm_100a).
+ *
+ * The reference has no FFI of its own: its hot path is the Rust
+ * crate software/rnghunt (lib.rs:12-21), the gateware generator blocks
+ * gateware/bbb/rng.py / prbs.py (whose numpy/Python models are the software
+ * contract) and software/clt-grng/clt-grng-evaluate.py.  Each entry point below
+ * names the reference interface it stands in for.  A Rust host binds these
+ * with a plain `extern "C"` block; the Python host mirror
+ * in basebandboard_b200/ binds them with ctypes.
+ *
+ * Conventions
+ *   - every call returns 0 on success or a negative BBB_E* code;
+ *     bbb_last_error(ctx) returns the message of the last failure on that ctx.
+ *   - one ctx per GPU per host thread; calls on one ctx are serialised by the
+ *     caller; no global mutable state; nothing throws across the boundary.
+ *   - generator state / URNG words: little-endian array of u64, state bit i is
+ *     word i/64 bit i%64 (bit i has weight 2^i, rng.py:135).
+ *   - recurrence matrix: CSR, row r is the XOR of x[taps[row_ptr[r]..row_ptr[r+1])]
+ *     (LUTOPT.from_packed, rng.py:42-55).
+ *   - rnghunt structures use the crate's layout: BinaryMatrix column-major,
+ *     word data[col*wpc + r/64], row r at bit 63 - r%64 (binary_matrix.rs:15-19);
+ *     polynomials MSbit-first with coefficient 0 = highest power
+ *     (binary_polynomial.rs:9-11, binary_vector.rs:25-31).
+ *   - sample indexing (DESIGN.md "definitions"): g[i] = clt(A^(i+1) . x0), i >= 0;
+ *     URNG word block i = A^(i+1) . x0; PRBS bit i = output of the i-th clock
+ *     from state0 (prbs.py:112-119).
+ *   - `*_dev` pointers are device pointers on the ctx's GPU (e.g. a torch
+ *     tensor's data_ptr); all other pointers are host memory.
+ *   - there is NO CPU fallback: with no usable GPU bbb_create fails.
+ */
+#ifndef BBB_B200_H
+#define BBB_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BBB_OK            0
+#define BBB_EINVAL       -1   /* bad argument                                   */
+#define BBB_ECUDA        -2   /* CUDA runtime error (message has the detail)    */
+#define BBB_ENOMEM       -3
+#define BBB_ESTATE       -4   /* call order (e.g. no recurrence loaded)         */
+#define BBB_EUNSUPPORTED -5
+
+#define BBB_MODEL_GATEWARE 0  /* CLTGRNG output truncated to log2(n) signed bits (rng.py:78,108) */
+#define BBB_MODEL_NUMPY    1  /* unwrapped value of the numpy model (rng.py:173-181)             */
+
+/* how far a candidate got through rnghunt.rs:36-44 / binary_polynomial.rs:178-212 */
+#define BBB_STAGE_DEGREE    0 /* Berlekamp-Massey degree != n (rnghunt.rs:39-41)          */
+#define BBB_STAGE_FILTER    1 /* zero constant term or even weight (:185-192)             */
+#define BBB_STAGE_ORDER     2 /* x^(2^n-1) != 1 (:198)                                    */
+#define BBB_STAGE_FACTOR    3 /* x^((2^n-1)/q) == 1 for a prime q (:204-208)              */
+#define BBB_STAGE_PRIMITIVE 4 /* accepted: "Found suitable recurrence matrix" (rnghunt.rs:44-45) */
+#define BBB_NSTAGES         5
+
+typedef struct bbb_ctx bbb_ctx;
+
+/* ---- context ----------------------------------------------------------- */
+int  bbb_version(void);
+/* Binds `device` (cudaSetDevice ordinal), creates the ctx's stream. */
+int  bbb_create(int device, bbb_ctx **out);
+void bbb_destroy(bbb_ctx *ctx);
+const char *bbb_last_error(const bbb_ctx *ctx);
+/* Device time (ms, CUDA events on the ctx's stream) of the kernels launched by
+ * the most recent call on this ctx, and how many of this library's kernels
+ * that call launched. */
+double   bbb_last_device_ms(const bbb_ctx *ctx);
+uint32_t bbb_last_launches(const bbb_ctx *ctx);
+/* Name of the kernel family the last CLT/LUTOPT call dispatched to
+ * ("clt256_fused", "generic", ...). */
+const char *bbb_last_kernel(const bbb_ctx *ctx);
+/* Block until everything queued on the ctx's stream has finished. */
+int  bbb_sync(bbb_ctx *ctx);
+
+/* ---- LUTOPT uniform RNG (gateware/bbb/rng.py:14-55) --------------------- */
+/* LUTOPT.from_packed(packed) (rng.py:42-55): n in [8,512], multiple of 8. */
+int bbb_lutopt_load(bbb_ctx *ctx, uint32_t n, const uint32_t *row_ptr, const uint16_t *taps);
+/* rng_recurrences.nN for N in {16,32,64,128,192,256} plus matrices/512. */
+int bbb_lutopt_load_shipped(bbb_ctx *ctx, uint32_t n);
+/* Copies the loaded recurrence out (sizes: n+1 and nnz); either may be NULL. */
+int bbb_lutopt_get(const bbb_ctx *ctx, uint32_t *n, uint32_t *nnz, uint32_t *row_ptr, uint16_t *taps);
+/* x_out = A^e . x_in (host-side GF(2) jump-ahead; e == 1 is one clock, rng.py:38-40). */
+int bbb_lutopt_jump(bbb_ctx *ctx, const uint64_t *x_in, uint64_t e, uint64_t *x_out);
+/* URNG words of clocks first+1 .. first+count (the `x` output of LUTOPT each
+ * clock, rng.py:27): out[i*nw + w], nw = ceil(n/64). */
+int bbb_lutopt_stream(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count,
+                      uint64_t *out_words);
+int bbb_lutopt_stream_dev(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count,
+                          uint64_t *out_words_dev);
+
+/* ---- CLT Gaussian RNG (rng.py:58-108; clt-grng-evaluate.py:8-21) ---------- */
+/* Fused generate + histogram + moments over g[first, first+count); nothing is
+ * stored.  hist has n bins (gateware) or n+1 (numpy), bin = g + n/2
+ * (clt-grng-evaluate.py:34: bins=n, range=(-n/2, n/2)); counts are ADDED to
+ * hist[], *sum (sum g) and *sumsq (sum g^2), any of which may be NULL.
+ * n must be a power of two (rng.py:73-74). */
+int bbb_clt_hist(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                 uint64_t *hist, int64_t *sum, uint64_t *sumsq);
+/* Same, result left on the device for an NCCL reduction: acc_dev[0..n] = hist
+ * (n+1 slots, slot n unused in gateware mode), acc_dev[n+1] = sum (two's
+ * complement), acc_dev[n+2] = sumsq.  ADDS into acc_dev; asynchronous on the
+ * ctx's stream (bbb_sync to wait). */
+int bbb_clt_hist_dev(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                     uint64_t *acc_dev);
+/* Materialised samples: out8[i] = g[first+i] as int8 (n <= 256), or
+ * out16[i] = g[first+i] * noise_var as int16 (tx.py:75-76; noise_var = 1 gives
+ * raw g).  Exactly one of out8/out16 is non-NULL. */
+int bbb_clt_stream(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                   uint32_t noise_var, int8_t *out8, int16_t *out16);
+int bbb_clt_stream_dev(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                       uint32_t noise_var, int8_t *out8_dev, int16_t *out16_dev);
+/* clt-grng-evaluate.py:18-21 from an integer histogram, in f64 with a fixed
+ * summation order: stats[0]=mean, [1]=variance (ddof=0), [2]=excess kurtosis,
+ * [3]=chi-square against N(0, n/4) bin probabilities, [4]=chi-square against the
+ * exact Binomial(n,1/2) law, [5]=theoretical variance n/4.  Pure host arithmetic. */
+int bbb_clt_stats(uint32_t n, uint32_t model, const uint64_t *hist, double *stats6);
+
+/* ---- PRBS (gateware/bbb/prbs.py) ---------------------------------------- */
+/* prbs.py:14 TAPS; returns 0 for an unsupported k. */
+uint32_t bbb_prbs_tap(uint32_t k);
+/* Packed PRBS-k bits [first_bit, first_bit+nbits) of the generator started at
+ * state0 (prbs.py:23-35 / :112-113): bit i -> out[(i-first_bit)/64] bit (i-first_bit)%64.
+ * nbits must be a multiple of 64. */
+int bbb_prbs_stream(bbb_ctx *ctx, uint32_t k, uint32_t state0, uint64_t first_bit, uint64_t nbits,
+                    uint64_t *out_words);
+int bbb_prbs_stream_dev(bbb_ctx *ctx, uint32_t k, uint32_t state0, uint64_t first_bit, uint64_t nbits,
+                        uint64_t *out_words_dev);
+
+/* PRBSErrorDetector registers (prbs.py:61-99). */
+typedef struct {
+    uint32_t bit_in, prbs, err_sr, reload_ctr;
+} bbb_det_state;
+
+typedef struct {
+    uint64_t err;           /* sum of `err` sampled after each clock edge (prbs.py:79)       */
+    uint64_t err_valid;     /* sum of err & !reload (the quantity prbs.py:158-163 compares)  */
+    uint64_t reload_events; /* edges at which err_count > k//2 fired (prbs.py:92-95)         */
+    uint64_t reload_cycles; /* sum of `reload` sampled after each clock edge (prbs.py:99)    */
+    uint64_t injected;      /* channel errors injected                                       */
+} bbb_det_counters;
+
+/* Generator(state0=1 advanced to first_bit) -> channel -> PRBSErrorDetector over
+ * bits [first_bit, first_bit+nbits).  Channel: err_m == 0 none, else Bernoulli
+ * 2^-err_m keyed (seed, absolute bit index).  `det` is the detector
+ * state on entry (NULL = reset state, prbs.py:62,80,90) and is advanced; counters
+ * are ADDED to *ctr. */
+int bbb_prbs_detect(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits, uint32_t err_m,
+                    uint64_t seed, bbb_det_state *det, bbb_det_counters *ctr);
+
+/* ---- rnghunt (software/rnghunt/src) ------------------------------------- */
+/* The body of the worker loop, rnghunt.rs:27-44, on `ncand` caller-supplied
+ * n x n matrices in BinaryMatrix layout (ncols*wpc u64 each, back to back; a
+ * Rust host passes a.data.as_ptr()).  stage[c] = BBB_STAGE_*.  poly_words (may
+ * be NULL) receives the Berlekamp-Massey polynomial of each candidate as
+ * ceil((n+1)/64) MSbit-first words, coefficient 0 = highest power, valid when
+ * the degree is n (zero otherwise). */
+int bbb_rnghunt_eval(bbb_ctx *ctx, uint32_t n, uint64_t ncand, const uint64_t *matrices,
+                     uint8_t *stage, uint64_t *poly_words);
+/* Candidate c of `seed` -- BinaryMatrix::random(n, n, [3,4,4,4,4,4,4,4])
+ * (binary_matrix.rs:81-101, rnghunt.rs:25) with the draws taken from the
+ * counter-based generator DESIGN.md defines -- generated on the device and
+ * returned in BinaryMatrix layout. */
+int bbb_rnghunt_candidate(bbb_ctx *ctx, uint32_t n, uint64_t seed, uint64_t c, uint64_t *matrix_words);
+/* Sweep candidates first, first+stride, ... (count of them) fully on the
+ * device: generate -> recur -> Berlekamp-Massey -> primitivity, with stream
+ * compaction between the stages.  best[] receives the (up to k) smallest
+ * accepted candidate indices in ascending order, *nfound how many were written,
+ * stage_counts[BBB_NSTAGES] is ADDED to; stage_out (may be NULL) gets one byte
+ * per candidate. */
+int bbb_rnghunt_sweep(bbb_ctx *ctx, uint32_t n, uint64_t seed, uint64_t first, uint64_t stride,
+                      uint64_t count, uint32_t k, uint64_t *best, uint32_t *nfound,
+                      uint64_t *stage_counts, uint8_t *stage_out);
+
+/* ---- measurement helpers ------------------------------------------------ */
+/* Dependent-free LOP3 issue micro-benchmark: returns thread-instructions/s
+ * (the integer-pipe roofline denominator). */
+int bbb_measure_lop3_peak(bbb_ctx *ctx, double *thread_instr_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BBB_B200_H */

@@ -1,0 +1,143 @@
+"""GPU parity: LUTOPT -> CLTGRNG through the C ABI vs the CPU oracle (bit-exact).
+
+Reference behaviour: gateware/bbb/rng.py:21-40 (LUTOPT), :70-108 (CLTGRNG), tx.py:75-76 (noise
+scaling), clt-grng-evaluate.py:18-21 (statistics).  The oracle is pinned to the reference's numpy
+models by tests/test_oracle_gen.py."""
+import numpy as np
+import pytest
+
+from basebandboard_b200 import recurrences
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from basebandboard_b200 import lib
+    c = lib.Context(0)
+    yield c
+    c.close()
+
+
+def _oracle_hist(orc, n, init, first, count, model):
+    r = orc.clt_run(recurrences.packed(n), init, first, count, model=model, threads=8 if count > 50000 else 1)
+    return r["hist"], r["sum"], r["sumsq"]
+
+
+@pytest.mark.parametrize("n", [16, 32, 64, 128, 256, 512])
+@pytest.mark.parametrize("count", [1, 31, 33, 64, 1000, 5000])
+def test_hist_small_counts_all_sizes(ctx, orc, n, count):
+    ctx.lutopt_load_shipped(n)
+    for model in (0, 1):
+        h, s, ss = ctx.clt_hist(1, 0, count, model)
+        oh, os_, oss = _oracle_hist(orc, n, 1, 0, count, model)
+        assert np.array_equal(h, oh)
+        assert (s, ss) == (os_, oss)
+        assert int(h.sum()) == count
+
+
+def test_hist_golden_first_samples(ctx, golden):
+    """First samples of the reference numpy model (tests/golden/golden.json)."""
+    for key in ("16", "32", "64", "128", "256"):
+        n = int(key)
+        g = golden["lutopt_clt"][key]
+        want = np.array(g["clt_numpy"])
+        ctx.lutopt_load_shipped(n)
+        got = ctx.clt_stream(g["init"], 0, len(want), model=1, noise_var=1)
+        assert np.array_equal(got.astype(np.int64), want)
+
+
+@pytest.mark.parametrize("n,count", [(256, 1 << 20), (32, 1 << 20), (16, 300000)])
+def test_hist_medium(ctx, orc, n, count):
+    """n=16/32 reach the +n/2 wrap corner (SURVEY 7 'hard parts') at these counts."""
+    ctx.lutopt_load_shipped(n)
+    for model in (0, 1):
+        h, s, ss = ctx.clt_hist(1, 0, count, model)
+        oh, os_, oss = _oracle_hist(orc, n, 1, 0, count, model)
+        assert np.array_equal(h, oh)
+        assert (s, ss) == (os_, oss)
+    if n == 16:
+        assert oh[16] > 0          # the corner really occurred (numpy-model bin n)
+
+
+def test_hist_offset_and_init(ctx, orc):
+    ctx.lutopt_load_shipped(256)
+    init = 0x123456789ABCDEF0FEDCBA9876543210 | (1 << 255)
+    first = (1 << 40) + 12345
+    h, s, ss = ctx.clt_hist(init, first, 70000, 0)
+    oh, os_, oss = _oracle_hist(orc, 256, init, first, 70000, 0)
+    assert np.array_equal(h, oh) and (s, ss) == (os_, oss)
+
+
+def test_hist_shard_consistency(ctx):
+    """hist(0..N) == sum of hist over shards, for shard sizes that change the stream geometry."""
+    ctx.lutopt_load_shipped(256)
+    N = 3_000_017
+    whole, s, ss = ctx.clt_hist(1, 0, N, 0)
+    for cuts in ([0, 1_000_000, 1_000_001, 2_500_000, N], [0, 17, 4096, N]):
+        acc = np.zeros_like(whole)
+        ts, tss = 0, 0
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            h, s1, s2 = ctx.clt_hist(1, a, b - a, 0)
+            acc += h
+            ts += s1
+            tss += s2
+        assert np.array_equal(acc, whole) and (ts, tss) == (s, ss)
+
+
+@pytest.mark.parametrize("n", [16, 64, 256])
+def test_sample_stream_int8_int16(ctx, orc, n):
+    ctx.lutopt_load_shipped(n)
+    count = 20011
+    ref = orc.clt_run(recurrences.packed(n), 1, 777, count, model=0, noise_var=8, want=("out8", "out16"))
+    got8 = ctx.clt_stream(1, 777, count, model=0)
+    got16 = ctx.clt_stream(1, 777, count, model=0, noise_var=8)
+    assert np.array_equal(got8, ref["out8"])
+    assert np.array_equal(got16, ref["out16"])          # tx.py:75-76
+
+
+@pytest.mark.parametrize("n", [16, 32, 192, 256, 512])
+def test_lutopt_word_stream(ctx, orc, n, golden):
+    ctx.lutopt_load_shipped(n)
+    count = 3000
+    ref = orc.clt_run(recurrences.packed(n), 1, 0, count, model=1, want=("words",))["words"]
+    got = ctx.lutopt_stream(1, 0, count)
+    assert np.array_equal(got.reshape(-1), ref)
+    if str(n) in golden["lutopt_clt"]:
+        from basebandboard_b200.lib import state_int
+        want = [int(h, 16) for h in golden["lutopt_clt"][str(n)]["states_hex"]]
+        assert [state_int(r) for r in got[:len(want)]] == want
+
+
+def test_custom_matrix_uses_generic_kernel(ctx, orc):
+    """A recurrence that is not one of the shipped ones goes through the data-driven kernel."""
+    rng = np.random.default_rng(5)
+    n = 64
+    packed = [sorted(rng.choice(n, size=rng.choice([3, 4]), replace=False).tolist()) for _ in range(n)]
+    ctx.lutopt_load(packed)
+    h, s, ss = ctx.clt_hist(0xDEADBEEFCAFEF00D, 5, 40000, 0)
+    r = orc.clt_run(packed, 0xDEADBEEFCAFEF00D, 5, 40000, model=0)
+    assert np.array_equal(h, r["hist"]) and (s, ss) == (r["sum"], r["sumsq"])
+    assert ctx.last_kernel == "generic"
+
+
+def test_jump_matches_oracle(ctx, orc):
+    ctx.lutopt_load_shipped(256)
+    for e in (0, 1, 2, 1000, (1 << 40) + 3, (1 << 64) - 1):
+        assert ctx.lutopt_jump(0xABCDEF0123456789 << 100 | 1, e) == \
+            orc.lutopt_jump(recurrences.packed(256), 0xABCDEF0123456789 << 100 | 1, e)
+
+
+def test_stats_match_numpy(ctx):
+    """clt-grng-evaluate.py:18-21: np.mean / np.var of the samples == stats from the histogram."""
+    from basebandboard_b200 import lib
+    ctx.lutopt_load_shipped(256)
+    n = 200000
+    samples = ctx.clt_stream(1, 0, n, model=0).astype(np.float64)
+    h, _, _ = ctx.clt_hist(1, 0, n, 0)
+    st = lib.clt_stats(256, h, 0)
+    assert st["mean"] == pytest.approx(np.mean(samples), rel=1e-9, abs=1e-12)
+    assert st["variance"] == pytest.approx(np.var(samples), rel=1e-9)
+    m = samples - samples.mean()
+    assert st["kurtosis"] == pytest.approx(np.mean(m ** 4) / np.var(samples) ** 2 - 3.0, rel=1e-9, abs=1e-12)
+    assert st["variance_theory"] == 64.0
