@@ -98,6 +98,7 @@ void bbb_ctx::begin_call()
 {
     last_ms = 0.0;
     last_launches = 0;
+    h2d_bytes = d2h_bytes = 0;
     cudaEventRecord(ev0, stream);
 }
 
@@ -148,7 +149,8 @@ int bbb_create(int device, bbb_ctx **out)
     if (prop.major < 10) { delete c; return BBB_EUNSUPPORTED; }   // built for sm_100a only
     c->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
+        cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
+        cudaEventCreate(&c->evt0) != cudaSuccess || cudaEventCreate(&c->evt1) != cudaSuccess) {
         delete c;
         return BBB_ECUDA;
     }
@@ -166,6 +168,8 @@ void bbb_destroy(bbb_ctx *c)
     if (c->d_taps) cudaFree(c->d_taps);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
+    cudaEventDestroy(c->evt0);
+    cudaEventDestroy(c->evt1);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -183,6 +187,28 @@ double bbb_last_device_ms(const bbb_ctx *c)
 
 uint32_t bbb_last_launches(const bbb_ctx *c) { return c ? c->last_launches : 0; }
 const char *bbb_last_kernel(const bbb_ctx *c) { return c ? c->last_kernel : "none"; }
+
+uint64_t bbb_last_h2d_bytes(const bbb_ctx *c) { return c ? c->h2d_bytes : 0; }
+uint64_t bbb_last_d2h_bytes(const bbb_ctx *c) { return c ? c->d2h_bytes : 0; }
+
+int bbb_timer_start(bbb_ctx *c)
+{
+    if (!c) return BBB_EINVAL;
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    BBB_CUDA(c, cudaEventRecord(c->evt0, c->stream));
+    return BBB_OK;
+}
+
+int bbb_timer_stop(bbb_ctx *c, double *ms)
+{
+    if (!c || !ms) return BBB_EINVAL;
+    BBB_CUDA(c, cudaEventRecord(c->evt1, c->stream));
+    BBB_CUDA(c, cudaEventSynchronize(c->evt1));
+    float f = 0.f;
+    BBB_CUDA(c, cudaEventElapsedTime(&f, c->evt0, c->evt1));
+    *ms = (double)f;
+    return BBB_OK;
+}
 
 int bbb_sync(bbb_ctx *c)
 {

@@ -35,7 +35,8 @@ struct HostMat {
 struct bbb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evt0 = nullptr, evt1 = nullptr;
+    uint64_t h2d_bytes = 0, d2h_bytes = 0;
     int sm_count = 0;
     std::string err;
     double last_ms = 0.0;
@@ -59,6 +60,17 @@ struct bbb_ctx {
     int fail(int code, const char *fmt, ...);
     int cuda_fail(cudaError_t e, const char *what);
     void *scratch(int slot, size_t bytes);   // nullptr on failure (err set)
+    // counted copies on the ctx's stream
+    cudaError_t h2d(void *dst, const void *src, size_t bytes)
+    {
+        h2d_bytes += bytes;
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream);
+    }
+    cudaError_t d2h(void *dst, const void *src, size_t bytes)
+    {
+        d2h_bytes += bytes;
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream);
+    }
     void begin_call();                       // resets timing counters, records ev0
     void end_call();                         // records ev1 (call bbb_sync before reading ms)
     const HostMat &pow2(uint32_t i);         // A^(2^i)

@@ -294,7 +294,7 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
                 c->pow2(logL + b).to_colmajor32(one);
                 memcpy(&all[(size_t)b * n * nw32], one.data(), one.size() * 4);
             }
-            if (nbits) BBB_CUDA(c, cudaMemcpyAsync(dJ, all.data(), all.size() * 4, cudaMemcpyHostToDevice, c->stream));
+            if (nbits) BBB_CUDA(c, c->h2d(dJ, all.data(), all.size() * 4));
             BBB_CUDA(c, cudaStreamSynchronize(c->stream));   // `all` is pageable host memory
         }
         uint32_t *d_planes = (uint32_t *)c->scratch(1, (size_t)n * T * 4);
@@ -384,7 +384,7 @@ int bbb_clt_hist(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count,
     rc = bbb_clt_hist_dev(c, x0, first, count, model, d_acc);
     if (rc) return rc;
     uint64_t h[BBB_MAX_N + 3];
-    BBB_CUDA(c, cudaMemcpyAsync(h, d_acc, (n + 3) * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+    BBB_CUDA(c, c->d2h(h, d_acc, (n + 3) * sizeof(uint64_t)));
     BBB_CUDA(c, cudaStreamSynchronize(c->stream));
     const uint32_t bins = n + (model == BBB_MODEL_NUMPY ? 1 : 0);
     if (hist) for (uint32_t b = 0; b < bins; b++) hist[b] += h[b];
@@ -423,7 +423,7 @@ int bbb_clt_stream(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t coun
     rc = bbb_clt_stream_dev(c, x0, first, count, model, noise_var, out8 ? (int8_t *)d : nullptr,
                             out16 ? (int16_t *)d : nullptr);
     if (rc) return rc;
-    BBB_CUDA(c, cudaMemcpyAsync(out8 ? (void *)out8 : (void *)out16, d, bytes, cudaMemcpyDeviceToHost, c->stream));
+    BBB_CUDA(c, c->d2h(out8 ? (void *)out8 : (void *)out16, d, bytes));
     BBB_CUDA(c, cudaStreamSynchronize(c->stream));
     return BBB_OK;
 }
@@ -451,7 +451,7 @@ int bbb_lutopt_stream(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t c
     if (!d) return BBB_ECUDA;
     rc = bbb_lutopt_stream_dev(c, x0, first, count, (uint64_t *)d);
     if (rc) return rc;
-    BBB_CUDA(c, cudaMemcpyAsync(out_words, d, bytes, cudaMemcpyDeviceToHost, c->stream));
+    BBB_CUDA(c, c->d2h(out_words, d, bytes));
     BBB_CUDA(c, cudaStreamSynchronize(c->stream));
     return BBB_OK;
 }

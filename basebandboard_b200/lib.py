@@ -52,6 +52,10 @@ SIGNATURES = {
     "bbb_last_launches": (C.c_uint32, [_ctx]),
     "bbb_last_kernel": (C.c_char_p, [_ctx]),
     "bbb_sync": (C.c_int, [_ctx]),
+    "bbb_last_h2d_bytes": (C.c_uint64, [_ctx]),
+    "bbb_last_d2h_bytes": (C.c_uint64, [_ctx]),
+    "bbb_timer_start": (C.c_int, [_ctx]),
+    "bbb_timer_stop": (C.c_int, [_ctx, _P(C.c_double)]),
     "bbb_lutopt_load": (C.c_int, [_ctx, C.c_uint32, _u32p, _u16p]),
     "bbb_lutopt_load_shipped": (C.c_int, [_ctx, C.c_uint32]),
     "bbb_lutopt_get": (C.c_int, [_ctx, _u32p, _u32p, _u32p, _u16p]),
@@ -160,6 +164,23 @@ class Context:
     # ---- measurement -----------------------------------------------------------------------
     def sync(self):
         self._check(self._L.bbb_sync(self._h))
+
+    def timer_start(self):
+        self._check(self._L.bbb_timer_start(self._h))
+
+    def timer_stop(self):
+        """Device milliseconds (CUDA events on the ctx's stream) since timer_start()."""
+        ms = C.c_double(0)
+        self._check(self._L.bbb_timer_stop(self._h, C.byref(ms)))
+        return float(ms.value)
+
+    @property
+    def last_h2d_bytes(self):
+        return int(self._L.bbb_last_h2d_bytes(self._h))
+
+    @property
+    def last_d2h_bytes(self):
+        return int(self._L.bbb_last_d2h_bytes(self._h))
 
     @property
     def last_device_ms(self):

@@ -1,0 +1,293 @@
+#!/usr/bin/env python3
+"""bench.py -- the headline measurement (BASELINE.json: bit-exact CLT-GRNG Gsamples/s/GPU).
+
+Workload (BASELINE.json configs[2], the configuration the metric is quoted on): LUTOPT(n256,
+init=1) -> CLTGRNG, 2^40 samples per GPU per step, fused generate + histogram + moments, no
+stream stored.  Rank r owns samples [r*2^40, (r+1)*2^40) (jump-ahead seeding, no data-path
+collective); the only exchange is one NCCL all-reduce of u64[259] (histogram | sum | sumsq) per step.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--log2-samples 40] [--impl reference]
+
+`value`     device-timed (CUDA events on the library's stream, max over ranks), results stay on device.
+`e2e`       the same step through the host-buffer C-ABI call bbb_clt_hist (host seed in, host
+            histogram/moments out, all copies inside the timed region).
+`roofline`  the fused kernel is bound by the integer ALU pipe (no HBM traffic, no tensor work):
+            achieved = samples/s * 986/32 LOP3-equivalent thread-instructions, peak =
+            LOP3 issue rate measured live by bbb_measure_lop3_peak.
+`cpu_baseline`  the CPU oracle port (oracle/, C, all host cores) on a bounded sample.
+The oracle is imported only for the cpu_baseline leg and for --impl reference.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_STATE = 256
+ALG_LOP3_PER_STEP32 = 986          # 492 (recurrence) + 494 (popcount tree) per 32 bit-sliced samples
+METRIC = "clt_grng_gsamples_per_s"
+UNIT = "Gsamples/s"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.2):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_evt.wait(self.period)
+
+    def finish(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def physical_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_port_rate(count, threads, first=0):
+    """Oracle port (oracle/gen.c orc_clt_run_mt) on `threads` host threads; returns samples/s."""
+    from oracle import oracle
+    from basebandboard_b200 import recurrences
+    packed = recurrences.packed(N_STATE)
+    oracle.clt_run(packed, 1, first, 1 << 16, model=0, threads=threads)       # warm
+    t0 = time.perf_counter()
+    oracle.clt_run(packed, 1, first, count, model=0, threads=threads)
+    return count / (time.perf_counter() - t0)
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path.  The reference (Rust
+    crate + numpy model lines) cannot be built or shipped (no Rust toolchain; /root/reference is
+    absent on the GPU box), so this times the oracle port on all host cores; each step is a bounded
+    sample of the same workload (same recurrence, seed, indexing, fused histogram + moments)."""
+    if rank != 0:
+        return
+    cores = host_cores()
+    cal = cpu_port_rate(1 << 21, cores)
+    per_step = max(1 << 20, int(cal * args.ref_step_seconds))
+    from oracle import oracle
+    from basebandboard_b200 import recurrences
+    packed = recurrences.packed(N_STATE)
+    for _ in range(args.warmup):
+        oracle.clt_run(packed, 1, 0, min(per_step, 1 << 20), model=0, threads=cores)
+    t0 = time.perf_counter()
+    for s in range(args.steps):
+        oracle.clt_run(packed, 1, s * per_step, per_step, model=0, threads=cores)
+    dt = time.perf_counter() - t0
+    val = args.steps * per_step / dt / 1e9
+    sample = "%d samples per step from sample index 0 (of the 2^%d per-GPU workload)" % (per_step, args.log2_samples)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32 (GF(2) bit ops)",
+        "data": "synthetic", "config": workload_config(args, world),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world):
+    return {
+        "workload": "clt-grng 2^%d samples/GPU fused generate+histogram+moments, no stream stored "
+                    "(BASELINE.json configs[2]); LUTOPT n256 init=1, gateware widths" % args.log2_samples,
+        "n": N_STATE, "log2_samples_per_gpu": args.log2_samples, "seed_init": 1,
+        "partition": "rank r owns sample indices [r*2^%d, (r+1)*2^%d)" % (args.log2_samples, args.log2_samples),
+        "collective": "all-reduce of u64[259] per step" if world > 1 else "none",
+        "l2": "no HBM-resident input: each step regenerates its seed planes (a few MB) and keeps "
+              "generator state on chip; nothing is re-read across steps, so no L2 flush applies",
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--log2-samples", type=int, default=40)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample length")
+    ap.add_argument("--ref-step-seconds", type=float, default=4.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from basebandboard_b200 import lib
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = lib.Context(local_rank)
+    ctx.lutopt_load_shipped(N_STATE)
+    count = 1 << args.log2_samples
+    first = rank * count
+    acc = torch.zeros(N_STATE + 3, dtype=torch.int64, device="cuda")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        acc.zero_()
+        torch.cuda.current_stream().synchronize()
+        ctx.clt_hist_dev(1, first, count, lib.MODEL_GATEWARE, acc.data_ptr())
+        launches = ctx.last_launches
+        if world > 1:
+            ctx.sync()
+            dist.all_reduce(acc)
+        return launches
+
+    lop3_peak = max(ctx.measure_lop3_peak() for _ in range(3))
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(physical_gpu_index(local_rank))
+    sampler.start()
+    launches = 0
+    kernel_ms = 0.0
+    t0 = time.perf_counter()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        launches += step_device()
+        kernel_ms += 0.0
+    dev_ms = ctx.timer_stop()
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.finish()
+    barrier()
+    # per-launch duration of the dominant kernel, from the library's own events around one call
+    acc.zero_()
+    torch.cuda.synchronize()
+    ctx.clt_hist_dev(1, first, count, lib.MODEL_GATEWARE, acc.data_ptr())
+    ctx.sync()
+    one_call_ms = ctx.last_device_ms
+    kernel_name = ctx.last_kernel
+    hist_dev = acc.cpu().numpy().astype("uint64")
+
+    # e2e: host buffers through bbb_clt_hist, copies inside the timed region
+    e2e_steps = max(1, min(args.steps, 2))
+    ctx.clt_hist(1, first, min(count, 1 << 24), lib.MODEL_GATEWARE)
+    barrier()
+    t1 = time.perf_counter()
+    h2d = d2h = 0
+    for _ in range(e2e_steps):
+        h, s1, s2 = ctx.clt_hist(1, first, count, lib.MODEL_GATEWARE)
+        h2d, d2h = ctx.last_h2d_bytes + 8 * ((N_STATE + 63) // 64), ctx.last_d2h_bytes
+    e2e_ms = (time.perf_counter() - t1) * 1e3 / e2e_steps
+    assert int(h.sum()) == count
+    if world == 1:
+        assert (hist_dev[:N_STATE] == h).all() and int(hist_dev[N_STATE + 2]) == s2, "device and host-API results differ"
+
+    t = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms, e2e_ms = [float(v) for v in t.cpu()]
+
+    if rank == 0:
+        total = world * count
+        value = total * args.steps / (dev_ms * 1e-3) / 1e9
+        per_gpu_rate = count / (one_call_ms * 1e-3)
+        achieved = per_gpu_rate * ALG_LOP3_PER_STEP32 / 32.0
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u32 (GF(2) bit ops)", "data": "synthetic",
+            "config": workload_config(args, world),
+            "wall_ms_per_step": wall_ms / args.steps,
+            "clocks": clocks,
+            "e2e": {"value": total / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "api": "bbb_clt_hist (host seed in, host hist/sum/sumsq out)"},
+            "gpu_launches": launches,
+            "roofline": {"bound": "alu", "kernel": kernel_name, "achieved": achieved / 1e12, "peak": lop3_peak / 1e12,
+                         "unit": "T thread-instr/s (LOP3-equivalent)", "frac": achieved / lop3_peak,
+                         "traffic": None, "launch_ms": one_call_ms,
+                         "note": "integer-pipe bound, not HBM/tensor: algorithmic work = 986 LOP3 per 32 "
+                                 "samples (492 recurrence + 494 popcount tree); peak = LOP3 issue rate measured "
+                                 "live on this GPU (bbb_measure_lop3_peak); HBM traffic ~0 B/sample"},
+            "result_check": {"hist_total": int(h.sum()), "sum": int(s1), "sumsq": int(s2)},
+        }
+        if not args.no_cpu_baseline:
+            cores = host_cores()
+            cal = cpu_port_rate(1 << 21, cores)
+            n_cpu = max(1 << 21, int(cal * args.cpu_seconds))
+            rate = cpu_port_rate(n_cpu, cores)
+            line["cpu_baseline"] = {"value": rate / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": "first %d samples of the workload (oracle/gen.c, %d threads)" % (n_cpu, cores)}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -76,6 +76,14 @@ uint32_t bbb_last_launches(const bbb_ctx *ctx);
 const char *bbb_last_kernel(const bbb_ctx *ctx);
 /* Block until everything queued on the ctx's stream has finished. */
 int  bbb_sync(bbb_ctx *ctx);
+/* Host<->device bytes the most recent call on this ctx copied (jump-ahead
+ * operators, seeds, results): what bench.py reports as h2d/d2h bytes per step. */
+uint64_t bbb_last_h2d_bytes(const bbb_ctx *ctx);
+uint64_t bbb_last_d2h_bytes(const bbb_ctx *ctx);
+/* Region timer: CUDA events on the ctx's stream around any number of calls.
+ * bbb_timer_stop waits for the stream and returns the device time in ms. */
+int  bbb_timer_start(bbb_ctx *ctx);
+int  bbb_timer_stop(bbb_ctx *ctx, double *ms);
 
 /* ---- LUTOPT uniform RNG (gateware/bbb/rng.py:14-55) --------------------- */
 /* LUTOPT.from_packed(packed) (rng.py:42-55): n in [8,512], multiple of 8. */
