@@ -191,6 +191,16 @@ const char *bbb_last_kernel(const bbb_ctx *c) { return c ? c->last_kernel : "non
 uint64_t bbb_last_h2d_bytes(const bbb_ctx *c) { return c ? c->h2d_bytes : 0; }
 uint64_t bbb_last_d2h_bytes(const bbb_ctx *c) { return c ? c->d2h_bytes : 0; }
 
+int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
+{
+    if (!c || !key) return BBB_EINVAL;
+    if (!strcmp(key, "clt_no_spec")) c->tune_no_spec = value != 0;
+    else if (!strcmp(key, "clt_spec_min_steps")) c->tune_spec_min_steps = value < 1 ? 1u : (uint32_t)value;
+    else if (!strcmp(key, "clt_spec_max_blocks")) c->tune_spec_max_blocks = value < 0 ? 0u : (uint32_t)value;
+    else return c->fail(BBB_EINVAL, "unknown tuning key %s", key);
+    return BBB_OK;
+}
+
 int bbb_timer_start(bbb_ctx *c)
 {
     if (!c) return BBB_EINVAL;
@@ -240,6 +250,8 @@ int bbb_lutopt_load(bbb_ctx *c, uint32_t n, const uint32_t *row_ptr, const uint1
         for (uint32_t j = row_ptr[r]; j < row_ptr[r + 1]; j++)
             c->A.row(r)[taps[j] >> 6] ^= 1ull << (taps[j] & 63);   // XOR: a repeated tap cancels
     c->Apow2.clear();
+    c->jump_key_L = 0;
+    c->jump_key_bits = 0;
     if (c->d_row_ptr) cudaFree(c->d_row_ptr);
     if (c->d_taps) cudaFree(c->d_taps);
     c->d_row_ptr = nullptr;

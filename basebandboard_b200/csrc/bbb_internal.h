@@ -48,6 +48,13 @@ struct bbb_ctx {
     std::vector<uint32_t> row_ptr;
     std::vector<uint16_t> taps;
     int shipped = 0;              // n of the shipped matrix this equals, else 0
+    // tuning knobs (bbb_set_tuning): tests use them to force a code path
+    int tune_no_spec = 0;               // 1: never use the specialised n256 kernel
+    uint32_t tune_spec_min_steps = 512; // fewest clocks per stream worth a specialised launch
+    uint32_t tune_spec_max_blocks = 0;  // 0: one CTA per SM
+    // cached jump-ahead operators on the device (scratch slot 0)
+    uint64_t jump_key_L = 0;
+    uint32_t jump_key_bits = 0;
     HostMat A;                    // dense A
     std::vector<HostMat> Apow2;   // A^(2^i), grown on demand
     uint32_t *d_row_ptr = nullptr;   // device copies for the generic kernel

@@ -234,15 +234,66 @@ static int launch_seed(bbb_ctx *c, const uint32_t *dJ, const SeedStart &xs, uint
     return BBB_OK;
 }
 
-// clt_spec.cu: returns 1 if a specialised kernel took the level, 0 if none applies, <0 on error
-int bbb_clt_spec_level(bbb_ctx *c, const SpecLevel &lv);
-int bbb_clt_spec_threads_per_sm(const bbb_ctx *c, bool hist_only, uint32_t *block);
+// clt_spec.cu
+int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only);
+int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model, const uint32_t *planes,
+                        unsigned long long *hist);
+
+// Uploads the jump-ahead operators A^(L*2^b), b < nbits, column-major 32-bit words, into scratch
+// slot 0 (kept across calls while (L, nbits) repeat).  Returns the device pointer or null.
+static uint32_t *upload_jump_ops(bbb_ctx *c, uint64_t L, uint32_t nbits)
+{
+    const uint32_t n = c->n, nw32 = (n + 31) / 32;
+    const size_t per = (size_t)n * nw32;
+    uint32_t *dJ = (uint32_t *)c->scratch(0, (nbits ? nbits : 1) * per * 4);
+    if (!dJ) return nullptr;
+    if (c->jump_key_L == L && c->jump_key_bits >= nbits && nbits) return dJ;
+    c->jump_key_L = 0;
+    if (!nbits) return dJ;
+    std::vector<uint32_t> all(nbits * per), one;
+    HostMat M;
+    if ((L & (L - 1)) == 0) {
+        uint32_t logL = 0;
+        while ((1ull << logL) < L) logL++;
+        for (uint32_t b = 0; b < nbits; b++) {
+            c->pow2(logL + b).to_colmajor32(one);
+            memcpy(&all[b * per], one.data(), per * 4);
+        }
+    } else {
+        c->power(L, M);
+        for (uint32_t b = 0; b < nbits; b++) {
+            M.to_colmajor32(one);
+            memcpy(&all[b * per], one.data(), per * 4);
+            if (b + 1 < nbits) HostMat::mul(M, M, M);
+        }
+    }
+    if (c->h2d(dJ, all.data(), all.size() * 4) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) {   // `all` is pageable host memory
+        c->cuda_fail(cudaGetLastError(), "upload jump operators");
+        return nullptr;
+    }
+    c->jump_key_L = L;
+    c->jump_key_bits = nbits;
+    return dJ;
+}
+
+static void advance_state(bbb_ctx *c, uint64_t *x, uint64_t clocks)
+{
+    for (uint32_t i = 0; i < 64 && (clocks >> i); i++)
+        if ((clocks >> i) & 1) c->pow2(i).apply(x, x);
+}
+
+static void to_seed(const uint64_t *x, uint32_t nw64, SeedStart &xs)
+{
+    for (uint32_t w = 0; w < BBB_MAX_NW32; w++)
+        xs.w[w] = w < 2 * nw64 ? (uint32_t)(x[w >> 1] >> (32 * (w & 1))) : 0u;
+}
 
 int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
                        uint64_t *d_hist, int8_t *d_out8, int16_t *d_out16, uint32_t noise_var,
                        uint32_t *d_out_words32)
 {
-    const uint32_t n = c->n, nw32 = (n + 31) / 32, nw64 = (n + 63) / 64;
+    const uint32_t n = c->n, nw64 = (n + 63) / 64;
     const bool want_clt = d_hist || d_out8 || d_out16;
     if (want_clt && (n & (n - 1))) return c->fail(BBB_EINVAL, "CLTGRNG needs n a power of two (rng.py:73-74), n=%u", n);
     if (d_out8 && n > 256) return c->fail(BBB_EINVAL, "int8 samples need n <= 256");
@@ -252,26 +303,57 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
     uint64_t xl[BBB_MAX_NW64] = {0};
     memcpy(xl, x0, nw64 * sizeof(uint64_t));
     if (n % 64) xl[nw64 - 1] &= (1ull << (n % 64)) - 1;
-    for (uint32_t i = 0; i < 64 && (first >> i); i++)
-        if ((first >> i) & 1) c->pow2(i).apply(xl, xl);
+    advance_state(c, xl, first);
 
     // generic-kernel geometry
     uint32_t Bg = 256;
     while (Bg > 32 && (size_t)8 * n * Bg > 200 * 1024) Bg -= 32;
     const size_t g_smem = (size_t)8 * n * Bg + (n + 1) * 4 + ((n + 2) & ~1u) * 2 + c->taps.size() * 2 + 16;
+    const uint64_t Sres = (uint64_t)c->sm_count * Bg * 32;
+    const uint32_t Lmin = 64;
 
     const bool hist_only = d_hist && !d_out8 && !d_out16 && !d_out_words32;
-    uint32_t spec_block = 0;
-    const int spec_tps = bbb_clt_spec_threads_per_sm(c, hist_only, &spec_block);
-    const uint32_t tps = spec_tps > 0 ? (uint32_t)spec_tps : Bg;
-    const uint64_t Sres = (uint64_t)c->sm_count * tps * 32;
-    const uint32_t Lmin = 64;
+    const uint64_t spb = (uint64_t)bbb_clt_spec_streams_per_block(c, hist_only);
 
     uint64_t done = 0;
     c->last_kernel = "generic";
     while (done < count) {
         const uint64_t rem = count - done;
-        // L = 2^k steps per stream, S streams (see file header)
+
+        // ---- specialised fused kernel: `blocks` CTAs x spb streams x L clocks, one wave ----
+        if (spb) {
+            const uint64_t max_blocks = c->tune_spec_max_blocks ? c->tune_spec_max_blocks : (uint64_t)c->sm_count;
+            uint64_t blocks = rem / (spb * c->tune_spec_min_steps);
+            if (blocks > max_blocks) blocks = max_blocks;
+            if (blocks >= 1) {
+                uint64_t L = rem / (blocks * spb);
+                if (L > (1ull << 26)) L = 1ull << 26;      // private u32 bins: 32 * L < 2^32
+                const uint64_t S = blocks * spb;
+                const uint32_t T = (uint32_t)(S / 32);
+                uint32_t nbits = 0;
+                while (nbits < 40 && ((S - 1) >> nbits)) nbits++;
+                uint32_t *dJ = upload_jump_ops(c, L, nbits);
+                if (!dJ) return BBB_ECUDA;
+                uint32_t *d_planes = (uint32_t *)c->scratch(1, (size_t)n * T * 4);
+                if (!d_planes) return BBB_ECUDA;
+                // the kernel takes the CLT of a stream's state BEFORE each clock: start one clock in
+                uint64_t x1[BBB_MAX_NW64];
+                memcpy(x1, xl, sizeof x1);
+                advance_state(c, x1, 1);
+                SeedStart xs;
+                to_seed(x1, nw64, xs);
+                int rc = launch_seed(c, dJ, xs, nbits, T, d_planes);
+                if (rc) return rc;
+                rc = bbb_clt_spec_launch(c, (uint32_t)blocks, (uint32_t)L, model, d_planes,
+                                         (unsigned long long *)d_hist);
+                if (rc) return rc;
+                advance_state(c, xl, S * L);
+                done += S * L;
+                continue;
+            }
+        }
+
+        // ---- data-driven kernel: S streams of L = 2^k clocks ----
         uint32_t logL = 0;
         if (rem >= Lmin) {
             logL = 6;
@@ -284,34 +366,15 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
         const uint32_t T = (uint32_t)T64;
         uint32_t nbits = 0;
         while (nbits < 40 && ((S - 1) >> nbits)) nbits++;
-
-        // jump operators A^(L*2^b), column-major 32-bit words
-        uint32_t *dJ = (uint32_t *)c->scratch(0, (size_t)(nbits ? nbits : 1) * n * nw32 * 4);
+        uint32_t *dJ = upload_jump_ops(c, L, nbits);
         if (!dJ) return BBB_ECUDA;
-        {
-            std::vector<uint32_t> all((size_t)nbits * n * nw32), one;
-            for (uint32_t b = 0; b < nbits; b++) {
-                c->pow2(logL + b).to_colmajor32(one);
-                memcpy(&all[(size_t)b * n * nw32], one.data(), one.size() * 4);
-            }
-            if (nbits) BBB_CUDA(c, c->h2d(dJ, all.data(), all.size() * 4));
-            BBB_CUDA(c, cudaStreamSynchronize(c->stream));   // `all` is pageable host memory
-        }
         uint32_t *d_planes = (uint32_t *)c->scratch(1, (size_t)n * T * 4);
         if (!d_planes) return BBB_ECUDA;
         SeedStart xs;
-        for (uint32_t w = 0; w < BBB_MAX_NW32; w++)
-            xs.w[w] = w < 2 * nw64 ? (uint32_t)(xl[w >> 1] >> (32 * (w & 1))) : 0u;
+        to_seed(xl, nw64, xs);
         int rc = launch_seed(c, dJ, xs, nbits, T, d_planes);
         if (rc) return rc;
-
-        SpecLevel lv;
-        lv.T = T; lv.logL = logL; lv.nvalid = S; lv.out_base = done; lv.model = model;
-        lv.noise_var = noise_var; lv.planes = d_planes; lv.hist = (unsigned long long *)d_hist;
-        lv.out8 = d_out8; lv.out16 = d_out16; lv.out_words = d_out_words32;
-        rc = bbb_clt_spec_level(c, lv);
-        if (rc < 0) return rc;
-        if (rc == 0) {
+        {
             GenericParams p;
             p.n = n; p.nnz = (uint32_t)c->taps.size(); p.T = T; p.L = (uint32_t)L; p.model = model;
             p.noise_var = noise_var; p.nw32out = 2 * nw64; p.nvalid = S; p.out_base = done;
@@ -326,10 +389,8 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
             c->last_launches++;
             BBB_CUDA(c, cudaGetLastError());
         }
-        // advance the level's start state by S*L clocks
         const uint64_t adv = S << logL;
-        for (uint32_t i = 0; i < 64 && (adv >> i); i++)
-            if ((adv >> i) & 1) c->pow2(i).apply(xl, xl);
+        advance_state(c, xl, adv);
         done += adv;
     }
     return BBB_OK;

@@ -54,6 +54,7 @@ SIGNATURES = {
     "bbb_sync": (C.c_int, [_ctx]),
     "bbb_last_h2d_bytes": (C.c_uint64, [_ctx]),
     "bbb_last_d2h_bytes": (C.c_uint64, [_ctx]),
+    "bbb_set_tuning": (C.c_int, [_ctx, C.c_char_p, C.c_int64]),
     "bbb_timer_start": (C.c_int, [_ctx]),
     "bbb_timer_stop": (C.c_int, [_ctx, _P(C.c_double)]),
     "bbb_lutopt_load": (C.c_int, [_ctx, C.c_uint32, _u32p, _u16p]),
@@ -164,6 +165,9 @@ class Context:
     # ---- measurement -----------------------------------------------------------------------
     def sync(self):
         self._check(self._L.bbb_sync(self._h))
+
+    def set_tuning(self, key, value):
+        self._check(self._L.bbb_set_tuning(self._h, key.encode(), int(value)))
 
     def timer_start(self):
         self._check(self._L.bbb_timer_start(self._h))

@@ -80,6 +80,9 @@ int  bbb_sync(bbb_ctx *ctx);
  * operators, seeds, results): what bench.py reports as h2d/d2h bytes per step. */
 uint64_t bbb_last_h2d_bytes(const bbb_ctx *ctx);
 uint64_t bbb_last_d2h_bytes(const bbb_ctx *ctx);
+/* Tuning knobs, for tests and experiments (results never depend on them):
+ *   "clt_no_spec" (0/1), "clt_spec_min_steps", "clt_spec_max_blocks". */
+int  bbb_set_tuning(bbb_ctx *ctx, const char *key, int64_t value);
 /* Region timer: CUDA events on the ctx's stream around any number of calls.
  * bbb_timer_stop waits for the stream and returns the device time in ms. */
 int  bbb_timer_start(bbb_ctx *ctx);

@@ -141,3 +141,43 @@ def test_stats_match_numpy(ctx):
     m = samples - samples.mean()
     assert st["kurtosis"] == pytest.approx(np.mean(m ** 4) / np.var(samples) ** 2 - 3.0, rel=1e-9, abs=1e-12)
     assert st["variance_theory"] == 64.0
+
+
+# ---- the specialised n256 kernel (clt_spec.cu) -------------------------------------------------
+@pytest.mark.parametrize("model", [0, 1])
+@pytest.mark.parametrize("blocks,min_steps,count", [(1, 40, 4096 * 57 + 123), (3, 33, 3 * 4096 * 70 + 4099),
+                                                   (0, 16, 5_000_011)])
+def test_spec256_matches_oracle(ctx, orc, model, blocks, min_steps, count):
+    """clt256_fused (straight-line bit-sliced kernel) + generic tail == oracle, both models; the
+    count is large enough that popcounts outside [96,160) occur (the atomic slow path)."""
+    ctx.lutopt_load_shipped(256)
+    ctx.set_tuning("clt_spec_min_steps", min_steps)
+    ctx.set_tuning("clt_spec_max_blocks", blocks)
+    try:
+        init = 1 if blocks != 3 else (0x5DEECE66D << 190) | 0xB
+        first = 0 if blocks != 3 else (1 << 41) + 9
+        h, s, ss = ctx.clt_hist(init, first, count, model)
+        assert ctx.last_kernel == "clt256_fused" or count < 4096 * min_steps
+        oh, os_, oss = _oracle_hist(orc, 256, init, first, count, model)
+        assert np.array_equal(h, oh)
+        assert (s, ss) == (os_, oss)
+        if count > 2_000_000:
+            assert int(oh[:96].sum() + oh[160:].sum()) > 0
+    finally:
+        ctx.set_tuning("clt_spec_min_steps", 512)
+        ctx.set_tuning("clt_spec_max_blocks", 0)
+
+
+def test_spec256_equals_generic_large(ctx):
+    """2^31 samples: specialised kernel == data-driven kernel (bit-exact histograms and moments)."""
+    ctx.lutopt_load_shipped(256)
+    a = ctx.clt_hist(1, 12345, 1 << 31, 0)
+    assert ctx.last_kernel == "clt256_fused"
+    ctx.set_tuning("clt_no_spec", 1)
+    try:
+        b = ctx.clt_hist(1, 12345, 1 << 31, 0)
+        assert ctx.last_kernel == "generic"
+    finally:
+        ctx.set_tuning("clt_no_spec", 0)
+    assert np.array_equal(a[0], b[0]) and a[1:] == b[1:]
+    assert int(a[0].sum()) == 1 << 31
