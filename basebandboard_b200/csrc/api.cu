@@ -166,6 +166,7 @@ void bbb_destroy(bbb_ctx *c)
     for (int i = 0; i < 8; i++) if (c->d_scratch[i]) cudaFree(c->d_scratch[i]);
     if (c->d_row_ptr) cudaFree(c->d_row_ptr);
     if (c->d_taps) cudaFree(c->d_taps);
+    bbb_prbs_free_tables(c);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaEventDestroy(c->evt0);
@@ -188,6 +189,8 @@ double bbb_last_device_ms(const bbb_ctx *c)
 uint32_t bbb_last_launches(const bbb_ctx *c) { return c ? c->last_launches : 0; }
 const char *bbb_last_kernel(const bbb_ctx *c) { return c ? c->last_kernel : "none"; }
 
+uint32_t bbb_last_rounds(const bbb_ctx *c) { return c ? c->last_rounds : 0; }
+
 uint64_t bbb_last_h2d_bytes(const bbb_ctx *c) { return c ? c->h2d_bytes : 0; }
 uint64_t bbb_last_d2h_bytes(const bbb_ctx *c) { return c ? c->d2h_bytes : 0; }
 
@@ -197,6 +200,8 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
     if (!strcmp(key, "clt_no_spec")) c->tune_no_spec = value != 0;
     else if (!strcmp(key, "clt_spec_min_steps")) c->tune_spec_min_steps = value < 1 ? 1u : (uint32_t)value;
     else if (!strcmp(key, "clt_spec_max_blocks")) c->tune_spec_max_blocks = value < 0 ? 0u : (uint32_t)value;
+    else if (!strcmp(key, "prbs_chunk_words")) c->tune_prbs_chunk_words = value < 0 ? 0u : (uint32_t)value;
+    else if (!strcmp(key, "prbs_stream_reps")) c->tune_prbs_stream_reps = value < 0 ? 0u : (uint32_t)value;
     else return c->fail(BBB_EINVAL, "unknown tuning key %s", key);
     return BBB_OK;
 }

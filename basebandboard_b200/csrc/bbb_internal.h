@@ -52,6 +52,12 @@ struct bbb_ctx {
     int tune_no_spec = 0;               // 1: never use the specialised n256 kernel
     uint32_t tune_spec_min_steps = 512; // fewest clocks per stream worth a specialised launch
     uint32_t tune_spec_max_blocks = 0;  // 0: one CTA per SM
+    uint32_t tune_prbs_chunk_words = 0; // 0: automatic detector chunk length (64-bit words)
+    uint32_t tune_prbs_stream_reps = 0; // 0: automatic stream-kernel repetitions per warp
+    uint32_t last_rounds = 0;           // kernel rounds of the last bbb_prbs_detect
+    // PRBS jump tables per k (prbs.cu), built on first use
+    void *prbs_host[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    void *prbs_dev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     // cached jump-ahead operators on the device (scratch slot 0)
     uint64_t jump_key_L = 0;
     uint32_t jump_key_bits = 0;
@@ -89,6 +95,9 @@ struct bbb_ctx {
         cudaError_t e__ = (call);                                 \
         if (e__ != cudaSuccess) return (ctx)->cuda_fail(e__, #call); \
     } while (0)
+
+// prbs.cu
+void bbb_prbs_free_tables(bbb_ctx *ctx);
 
 // clt.cu
 int bbb_clt_run_device(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,

@@ -1,0 +1,643 @@
+// prbs.cu -- PRBS generator and PRBSErrorDetector on the device (gateware/bbb/prbs.py).
+//
+//   PRBS (prbs.py:23-35, model :112-113): k-bit state s (reset 1), output bit
+//   b = s[k-1] ^ s[tap-1], s' = ((s << 1) | b) & (2^k - 1).  The state at bit position p is the
+//   window of the last k output bits, s_p[i] = b[p-1-i], and b[t] = b[t-k] ^ b[t-tap].
+//
+// Two facts carry the device design (DESIGN.md "PRBS path"):
+//   * squaring the characteristic polynomial over GF(2) six times gives the same recurrence on
+//     64-bit WORDS of the packed stream, W[j] = W[j-k] ^ W[j-tap] (and on any power-of-two word
+//     stride), so the steady state is one 64-bit XOR per stored word: HBM-write bound;
+//   * any position is reached by GF(2) jump-ahead: the host precomputes the k x k matrices M^(2^e)
+//     of the one-bit step once per k, a thread applies those selected by the bits of its offset.
+//
+// The detector (prbs.py:43-99) is a sequential state machine with data-dependent reloads.  The bit
+// range is cut into chunks, one thread each; a chunk first runs from the state the detector has
+// when it is locked and no reload is pending (a function of the k+1 preceding channel bits only),
+// then chunks whose predecessor ended in a different state are re-run from that state until
+// nothing changes (fixed point == the sequential result, exactly).  Inside a chunk, 64-cycle
+// words during which the detector provably stays locked and cannot fire are retired with a few
+// word-wide operations; everything else is clocked bit by bit.
+#include "bbb_internal.h"
+
+// ---------------------------------------------------------------------------
+// tables
+// ---------------------------------------------------------------------------
+struct PrbsTables {
+    uint32_t pw[64][32];   // pw[e][i] = M^(2^e) . e_i : columns of the jump matrices
+    uint64_t col64[32];    // the 64 output bits that follow state e_i (bit t of the word = b[p+t])
+};
+
+static inline uint32_t host_prbs_step(uint32_t k, uint32_t tap, uint32_t s)
+{
+    const uint32_t b = ((s >> (k - 1)) ^ (s >> (tap - 1))) & 1u;   // prbs.py:29 / :112
+    return ((s << 1) | b) & (uint32_t)((1ull << k) - 1);           // prbs.py:30 / :113
+}
+
+// the state one clock earlier (the LFSR step is a bijection)
+static inline uint32_t host_prbs_unstep(uint32_t k, uint32_t tap, uint32_t s)
+{
+    const uint32_t hi = (s ^ (s >> tap)) & 1u;   // s_prev[k-1] = b ^ s_prev[tap-1] = s[0] ^ s[tap]
+    return (s >> 1) | (hi << (k - 1));
+}
+
+static inline uint32_t host_matvec(const uint32_t *cols, uint32_t k, uint32_t x)
+{
+    uint32_t y = 0;
+    for (uint32_t i = 0; i < k; i++)
+        if ((x >> i) & 1u) y ^= cols[i];
+    return y;
+}
+
+static void build_tables(uint32_t k, uint32_t tap, PrbsTables &t)
+{
+    memset(&t, 0, sizeof t);
+    for (uint32_t i = 0; i < k; i++) t.pw[0][i] = host_prbs_step(k, tap, 1u << i);
+    for (uint32_t e = 1; e < 64; e++)
+        for (uint32_t i = 0; i < k; i++) t.pw[e][i] = host_matvec(t.pw[e - 1], k, t.pw[e - 1][i]);
+    for (uint32_t i = 0; i < k; i++) {
+        uint32_t s = 1u << i;
+        uint64_t w = 0;
+        for (uint32_t b = 0; b < 64; b++) {
+            w |= (uint64_t)(((s >> (k - 1)) ^ (s >> (tap - 1))) & 1u) << b;
+            s = host_prbs_step(k, tap, s);
+        }
+        t.col64[i] = w;
+    }
+}
+
+static uint32_t host_jump(const PrbsTables &t, uint32_t k, uint32_t s, uint64_t delta)
+{
+    for (uint32_t e = 0; delta; e++, delta >>= 1)
+        if (delta & 1) s = host_matvec(t.pw[e], k, s);
+    return s;
+}
+
+static int prbs_slot(uint32_t k)
+{
+    switch (k) {
+    case 7: return 0; case 9: return 1; case 11: return 2; case 15: return 3;
+    case 20: return 4; case 23: return 5; case 31: return 6; default: return -1;
+    }
+}
+
+// Host + device copies of the tables for k, built on first use and kept by the ctx.
+static int get_tables(bbb_ctx *c, uint32_t k, const PrbsTables **host, const PrbsTables **dev)
+{
+    const int slot = prbs_slot(k);
+    if (slot < 0) return c->fail(BBB_EINVAL, "k=%u is not one of prbs.py:14's TAPS keys", k);
+    if (!c->prbs_host[slot]) {
+        PrbsTables *h = new (std::nothrow) PrbsTables;
+        if (!h) return c->fail(BBB_ENOMEM, "out of memory");
+        build_tables(k, bbb_prbs_tap(k), *h);
+        void *d = nullptr;
+        cudaError_t e = cudaMalloc(&d, sizeof(PrbsTables));
+        if (e == cudaSuccess) e = cudaMemcpy(d, h, sizeof(PrbsTables), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            if (d) cudaFree(d);
+            delete h;
+            return c->cuda_fail(e, "upload PRBS tables");
+        }
+        c->prbs_host[slot] = h;
+        c->prbs_dev[slot] = d;
+    }
+    *host = (const PrbsTables *)c->prbs_host[slot];
+    *dev = (const PrbsTables *)c->prbs_dev[slot];
+    return BBB_OK;
+}
+
+void bbb_prbs_free_tables(bbb_ctx *c)
+{
+    for (int i = 0; i < 8; i++) {
+        if (c->prbs_host[i]) delete (PrbsTables *)c->prbs_host[i];
+        if (c->prbs_dev[i]) cudaFree(c->prbs_dev[i]);
+        c->prbs_host[i] = nullptr;
+        c->prbs_dev[i] = nullptr;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------
+struct PrbsShared {
+    uint32_t pw[64][32];
+    uint64_t col64[32];
+};
+
+template <int K>
+__device__ __forceinline__ void load_tables(PrbsShared &sh, const PrbsTables *__restrict__ t)
+{
+    const uint32_t *src = (const uint32_t *)t;
+    uint32_t *dst = (uint32_t *)&sh;
+    for (uint32_t i = threadIdx.x; i < sizeof(PrbsTables) / 4; i += blockDim.x) dst[i] = src[i];
+    __syncthreads();
+}
+
+template <int K>
+__device__ __forceinline__ uint32_t matvec(const uint32_t *cols, uint32_t x)
+{
+    uint32_t y = 0;
+#pragma unroll
+    for (int i = 0; i < K; i++) y ^= (0u - ((x >> i) & 1u)) & cols[i];
+    return y;
+}
+
+template <int K>
+__device__ __forceinline__ uint32_t jump(const PrbsShared &sh, uint32_t s, uint64_t delta)
+{
+    for (uint32_t e = 0; delta; e++, delta >>= 1)
+        if (delta & 1) s = matvec<K>(sh.pw[e], s);
+    return s;
+}
+
+// the 64 bits b[p .. p+63] that follow state s_p
+template <int K>
+__device__ __forceinline__ uint64_t word_of(const PrbsShared &sh, uint32_t s)
+{
+    uint64_t w = 0;
+#pragma unroll
+    for (int i = 0; i < K; i++) w ^= (0ull - (uint64_t)((s >> i) & 1u)) & sh.col64[i];
+    return w;
+}
+
+// s_{p+64} from the word b[p .. p+63]: s[i] = b[p+63-i]
+template <int K>
+__device__ __forceinline__ uint32_t state_after(uint64_t w)
+{
+    return __brev((uint32_t)(w >> 32)) & (uint32_t)((1ull << K) - 1);
+}
+
+// ---------------------------------------------------------------------------
+// stream kernel: packed bits, one warp per chunk, lane l owns words VEC*l .. VEC*l+VEC-1 of
+// every group of 32*VEC words; K groups of history stay in registers.
+// ---------------------------------------------------------------------------
+template <int K, int TAP, int VEC>
+__global__ void __launch_bounds__(128)
+prbs_stream_kernel(const PrbsTables *__restrict__ tab, uint32_t s_first, uint64_t nwords, uint32_t reps,
+                   uint64_t *__restrict__ out)
+{
+    __shared__ PrbsShared sh;
+    load_tables<K>(sh, tab);
+    constexpr uint32_t GW = 32 * VEC;                    // words per warp step
+    constexpr uint32_t LOG_GW = VEC == 2 ? 6 : 5;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint64_t chunk_words = (uint64_t)GW * K * reps;
+    const uint64_t cbase = warp * chunk_words;
+    if (cbase >= nwords) return;
+    uint64_t h[K][VEC];
+    {
+        uint32_t s = jump<K>(sh, s_first, (cbase + (uint64_t)VEC * lane) << 6);
+#pragma unroll
+        for (int m = 0; m < K; m++) {
+            uint32_t sv = s;
+#pragma unroll
+            for (int v = 0; v < VEC; v++) {
+                h[m][v] = word_of<K>(sh, sv);
+                sv = state_after<K>(h[m][v]);
+            }
+            s = matvec<K>(sh.pw[6 + LOG_GW], s);          // GW words further on
+        }
+    }
+    uint64_t j = cbase + (uint64_t)VEC * lane;
+    const bool whole = cbase + chunk_words <= nwords;     // warp-uniform
+    for (uint32_t r = 0; r < reps; r++) {
+#pragma unroll
+        for (int m = 0; m < K; m++) {
+            if (r) {
+#pragma unroll
+                for (int v = 0; v < VEC; v++) h[m][v] ^= h[(m + K - TAP) % K][v];   // W[j] = W[j-k] ^ W[j-tap]
+            }
+            if (VEC == 2) {
+                if (whole || j + 1 < nwords)
+                    __stcs((ulonglong2 *)(out + j), make_ulonglong2(h[m][0], h[m][VEC - 1]));
+                else if (j < nwords)
+                    out[j] = h[m][0];
+            } else {
+                if (whole || j < nwords) __stcs(out + j, h[m][0]);
+            }
+            j += GW;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// detector
+// ---------------------------------------------------------------------------
+struct DetectParams {
+    const PrbsTables *tab;
+    uint32_t s_m1;             // generator state at bit first_bit - 1
+    uint32_t err_m;
+    uint64_t seed, first_bit, nbits;
+    uint32_t chunk_words, nchunks, round;
+    uint4 det0;                // detector state on entry (chunk 0)
+    uint4 *start_used;         // [nchunks]
+    uint4 *end_prev, *end_cur; // [nchunks] double-buffered end states
+    unsigned long long *ctr;   // [5][nchunks]
+    uint32_t *changed;
+};
+
+// DESIGN.md "channel": Bernoulli(2^-m) error word for absolute bits [64W, 64W+64): the AND of m
+// splitmix64-finalised counters keyed (seed, W, draw).
+__device__ __forceinline__ uint64_t mix64(uint64_t z)
+{
+    z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull;
+    z ^= z >> 27; z *= 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return z;
+}
+
+__device__ __forceinline__ uint64_t err_word(uint64_t seed, uint64_t W, uint32_t m)
+{
+    uint64_t e = ~0ull;
+    for (uint32_t j = 0; j < m; j++) e &= mix64(seed + ((W << 4) | j) * 0x9E3779B97F4A7C15ull);
+    return e;
+}
+
+// error bits of the 64 channel bits starting at absolute bit `a`
+__device__ __forceinline__ uint64_t err_bits_at(uint64_t seed, uint64_t a, uint32_t m)
+{
+    if (!m) return 0;
+    const uint32_t sh = (uint32_t)(a & 63);
+    uint64_t e = err_word(seed, a >> 6, m) >> sh;
+    if (sh) e |= err_word(seed, (a >> 6) + 1, m) << (64 - sh);
+    return e;
+}
+
+template <int K, int TAP>
+__global__ void __launch_bounds__(128)
+prbs_detect_kernel(DetectParams p)
+{
+    __shared__ PrbsShared sh;
+    __shared__ uint64_t ring[K][128];
+    load_tables<K>(sh, p.tab);
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= p.nchunks) return;
+    constexpr uint32_t MASK = (uint32_t)((1ull << K) - 1);
+    const uint32_t tid = threadIdx.x;
+
+    const uint64_t w0 = (uint64_t)c * p.chunk_words;              // first word of the chunk
+    const uint64_t bit0 = w0 << 6;                                 // relative to first_bit
+    uint64_t bits_left = p.nbits - bit0;
+    if (bits_left > ((uint64_t)p.chunk_words << 6)) bits_left = (uint64_t)p.chunk_words << 6;
+
+    // ---- which start state? ----
+    uint4 start;
+    bool have_start = false;
+    if (c == 0) { start = p.det0; have_start = true; }
+    else if (p.round > 0) { start = p.end_prev[c - 1]; have_start = true; }
+    if (p.round > 0) {
+        const uint4 u = p.start_used[c];
+        if (u.x == start.x && u.y == start.y && u.z == start.z && u.w == start.w) {
+            p.end_cur[c] = p.end_prev[c];
+            return;
+        }
+        *p.changed = 1u;
+    }
+
+    // ---- generator: states either side of the chunk start, first K words ----
+    const uint32_t s_pm1 = jump<K>(sh, p.s_m1, bit0);
+    const uint32_t s_p = matvec<K>(sh.pw[0], s_pm1);
+    {
+        uint32_t s = s_p;
+#pragma unroll 1
+        for (int m = 0; m < K; m++) {
+            const uint64_t w = word_of<K>(sh, s);
+            ring[m][tid] = w;
+            s = state_after<K>(w);
+        }
+    }
+    // "previous word" whose top K+1 bits encode b[p-1] (bit 63) and s_{p-1}[i] (bit 62-i)
+    uint64_t wprev = __brevll(((uint64_t)s_pm1 << 1) | (uint64_t)(s_p & 1u));
+
+    if (!have_start) {
+        // locked, nothing pending: bit_in = received b[p-1], prbs = s_{p-1}, err_sr = the error bits
+        // of the K cycles before, reload_ctr = 0
+        const uint64_t eprev = err_bits_at(p.seed, p.first_bit + bit0 - 64, p.err_m);
+        start.x = (uint32_t)((wprev ^ eprev) >> 63);
+        start.y = s_pm1;
+        start.z = (uint32_t)__brevll(eprev << 1) & MASK;
+        start.w = 0;
+    }
+    p.start_used[c] = start;
+    uint32_t bit_in = start.x, prbs = start.y, err_sr = start.z, ctr = start.w;
+    unsigned long long n_err = 0, n_valid = 0, n_fire = 0, n_rcyc = 0, n_inj = 0;
+
+    uint32_t pos = 0, tpos = K - TAP;    // ring slots of W[j-K] and W[j-TAP]
+    const uint64_t nwords = (bits_left + 63) >> 6;
+    for (uint64_t j = 0; j < nwords; j++) {
+        uint64_t w;
+        if (j < (uint64_t)K) w = ring[pos][tid];
+        else { w = ring[pos][tid] ^ ring[tpos][tid]; ring[pos][tid] = w; }
+        pos = pos + 1 == K ? 0 : pos + 1;
+        tpos = tpos + 1 == K ? 0 : tpos + 1;
+
+        const uint32_t nb = bits_left - (j << 6) >= 64 ? 64u : (uint32_t)(bits_left - (j << 6));
+        uint64_t e = err_bits_at(p.seed, p.first_bit + bit0 + (j << 6), p.err_m);
+        if (nb < 64) e &= (1ull << nb) - 1;
+        n_inj += __popcll(e);
+        const uint64_t r = w ^ e;                                     // received bits
+
+        const uint32_t prbs_exp = __brev((uint32_t)(wprev >> 31)) & MASK;
+        const uint32_t pend = bit_in ^ (uint32_t)(wprev >> 63);
+        const uint32_t worst = __popc(err_sr) + pend + __popcll(e & 0x7fffffffffffffffull);
+        if (nb == 64 && ctr == 0 && prbs == prbs_exp && worst <= K / 2) {
+            // locked for the whole word and no window of K cycles can exceed K/2 errors: err pulses
+            // are exactly the channel errors, no reload
+            const uint32_t ne = __popcll(e);
+            n_err += ne;
+            n_valid += ne;
+            err_sr = (uint32_t)__brevll(e << 1) & MASK;
+            bit_in = (uint32_t)(r >> 63);
+            prbs = __brev((uint32_t)(w >> 31)) & MASK;
+        } else {
+            for (uint32_t i = 0; i < nb; i++) {
+                // combinational values before the edge (prbs.py:67,75-76,79,84-86,99)
+                const uint32_t fb = ((prbs >> (K - 1)) ^ (prbs >> (TAP - 1))) & 1u;
+                const uint32_t reload = ctr != 0;
+                const uint32_t prbs_in = reload ? bit_in : fb;
+                const uint32_t err = bit_in ^ fb;
+                const bool fired = __popc(err_sr) > K / 2;
+                // the edge (prbs.py:66,68,81,91-98)
+                prbs = ((prbs << 1) | prbs_in) & MASK;
+                err_sr = ((err_sr << 1) | err) & MASK;
+                bit_in = (uint32_t)(r >> i) & 1u;
+                if (fired) { ctr = K + K / 2; err_sr = 0; n_fire++; }
+                else if (reload) ctr--;
+                // outputs after the edge, as prbs.py:150-151 samples them
+                const uint32_t fb2 = ((prbs >> (K - 1)) ^ (prbs >> (TAP - 1))) & 1u;
+                const uint32_t err2 = bit_in ^ fb2;
+                const uint32_t rl2 = ctr != 0;
+                n_err += err2;
+                n_valid += err2 & (rl2 ^ 1u);
+                n_rcyc += rl2;
+            }
+        }
+        wprev = w;
+    }
+    p.end_cur[c] = make_uint4(bit_in, prbs, err_sr, ctr);
+    p.ctr[0 * (size_t)p.nchunks + c] = n_err;
+    p.ctr[1 * (size_t)p.nchunks + c] = n_valid;
+    p.ctr[2 * (size_t)p.nchunks + c] = n_fire;
+    p.ctr[3 * (size_t)p.nchunks + c] = n_rcyc;
+    p.ctr[4 * (size_t)p.nchunks + c] = n_inj;
+}
+
+// out[0..4] = column sums of ctr[5][n]; out[5..8] = end state of the last chunk
+__global__ void __launch_bounds__(256)
+prbs_detect_reduce_kernel(const unsigned long long *__restrict__ ctr, const uint4 *__restrict__ end, uint32_t n,
+                          unsigned long long *__restrict__ out)
+{
+    __shared__ unsigned long long s[256];
+    const uint32_t q = blockIdx.x;   // counter index
+    unsigned long long a = 0;
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) a += ctr[(size_t)q * n + i];
+    s[threadIdx.x] = a;
+    __syncthreads();
+    for (uint32_t st = 128; st; st >>= 1) {
+        if (threadIdx.x < st) s[threadIdx.x] += s[threadIdx.x + st];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        out[q] = s[0];
+        if (q == 0) {
+            const uint4 e = end[n - 1];
+            out[5] = e.x; out[6] = e.y; out[7] = e.z; out[8] = e.w;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------
+template <int VEC>
+static int launch_stream(bbb_ctx *c, uint32_t k, const PrbsTables *dtab, uint32_t s_first, uint64_t nwords,
+                         uint64_t *d_out)
+{
+    // one warp per chunk of 32*VEC*k*reps words; a single wave of sm_count*12 warps when the range is
+    // long enough, so every warp amortises its jump-ahead over the same number of stores
+    const uint64_t unit = (uint64_t)32 * VEC * k;
+    uint64_t reps = (nwords + unit * c->sm_count * 12 - 1) / (unit * c->sm_count * 12);
+    if (c->tune_prbs_stream_reps) reps = c->tune_prbs_stream_reps;
+    if (reps < 1) reps = 1;
+    if (reps > 1u << 20) reps = 1u << 20;
+    const uint64_t warps = (nwords + unit * reps - 1) / (unit * reps);
+    const uint64_t blocks = (warps + 3) / 4;
+    if (blocks > 0x7fffffffull) return c->fail(BBB_EINVAL, "range too large");
+#define PRBS_CASE(K, TAP) \
+    case K: prbs_stream_kernel<K, TAP, VEC><<<(uint32_t)blocks, 128, 0, c->stream>>>(dtab, s_first, nwords, \
+                                                                                      (uint32_t)reps, d_out); break
+    switch (k) {
+        PRBS_CASE(7, 6); PRBS_CASE(9, 5); PRBS_CASE(11, 9); PRBS_CASE(15, 14);
+        PRBS_CASE(20, 3); PRBS_CASE(23, 18); PRBS_CASE(31, 28);
+    default: return c->fail(BBB_EINVAL, "bad k");
+    }
+#undef PRBS_CASE
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    return BBB_OK;
+}
+
+static int check_prbs_args(bbb_ctx *c, uint32_t k, uint32_t state0)
+{
+    if (!c) return BBB_EINVAL;
+    if (!bbb_prbs_tap(k)) return c->fail(BBB_EINVAL, "k=%u is not one of prbs.py:14's TAPS keys", k);
+    if (state0 >> k) return c->fail(BBB_EINVAL, "state0 has more than k bits");
+    return BBB_OK;
+}
+
+extern "C" {
+
+uint32_t bbb_prbs_tap(uint32_t k)
+{
+    switch (k) {   // prbs.py:14
+    case 7: return 6; case 9: return 5; case 11: return 9; case 15: return 14;
+    case 20: return 3; case 23: return 18; case 31: return 28; default: return 0;
+    }
+}
+
+int bbb_prbs_stream_dev(bbb_ctx *c, uint32_t k, uint32_t state0, uint64_t first_bit, uint64_t nbits,
+                        uint64_t *out_words_dev)
+{
+    int rc = check_prbs_args(c, k, state0);
+    if (rc) return rc;
+    if (nbits % 64) return c->fail(BBB_EINVAL, "nbits must be a multiple of 64");
+    if (!out_words_dev && nbits) return c->fail(BBB_EINVAL, "out is null");
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    const PrbsTables *ht, *dt;
+    rc = get_tables(c, k, &ht, &dt);
+    if (rc) return rc;
+    c->begin_call();
+    c->last_kernel = "prbs_stream";
+    if (nbits) {
+        const uint32_t s_first = host_jump(*ht, k, state0, first_bit);
+        if (((uintptr_t)out_words_dev & 15) == 0) rc = launch_stream<2>(c, k, dt, s_first, nbits / 64, out_words_dev);
+        else rc = launch_stream<1>(c, k, dt, s_first, nbits / 64, out_words_dev);
+        if (rc) return rc;
+    }
+    c->end_call();
+    return BBB_OK;
+}
+
+int bbb_prbs_stream(bbb_ctx *c, uint32_t k, uint32_t state0, uint64_t first_bit, uint64_t nbits,
+                    uint64_t *out_words)
+{
+    int rc = check_prbs_args(c, k, state0);
+    if (rc) return rc;
+    if (!out_words && nbits) return c->fail(BBB_EINVAL, "out is null");
+    const size_t bytes = (size_t)(nbits / 64) * 8;
+    void *d = c->scratch(4, bytes ? bytes : 1);
+    if (!d) return BBB_ECUDA;
+    rc = bbb_prbs_stream_dev(c, k, state0, first_bit, nbits, (uint64_t *)d);
+    if (rc) return rc;
+    if (bytes) BBB_CUDA(c, c->d2h(out_words, d, bytes));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return BBB_OK;
+}
+
+// splitmix64-keyed channel, host copy (bbb_prbs_spec_state only)
+static uint64_t host_mix64(uint64_t z)
+{
+    z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull;
+    z ^= z >> 27; z *= 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return z;
+}
+
+static uint64_t host_err_bits_at(uint64_t seed, uint64_t a, uint32_t m)
+{
+    if (!m) return 0;
+    uint64_t w[2];
+    for (int q = 0; q < 2; q++) {
+        uint64_t e = ~0ull;
+        for (uint32_t j = 0; j < m; j++) e &= host_mix64(seed + ((((a >> 6) + q) << 4) | j) * 0x9E3779B97F4A7C15ull);
+        w[q] = e;
+    }
+    const uint32_t sh = (uint32_t)(a & 63);
+    return sh ? (w[0] >> sh) | (w[1] << (64 - sh)) : w[0];
+}
+
+static uint64_t host_brev64(uint64_t x)
+{
+    uint64_t y = 0;
+    for (int i = 0; i < 64; i++) y |= ((x >> i) & 1ull) << (63 - i);
+    return y;
+}
+
+int bbb_prbs_spec_state(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint32_t err_m, uint64_t seed,
+                        bbb_det_state *det)
+{
+    int rc = check_prbs_args(c, k, 0);
+    if (rc) return rc;
+    if (!det) return c->fail(BBB_EINVAL, "det is null");
+    if (err_m > 16) return c->fail(BBB_EINVAL, "err_m must be 0..16");
+    if (first_bit < 64) return c->fail(BBB_EINVAL, "first_bit must be >= 64 (the detector starts from reset at 0)");
+    const PrbsTables *ht, *dt;
+    rc = get_tables(c, k, &ht, &dt);
+    if (rc) return rc;
+    const uint32_t tap = bbb_prbs_tap(k), mask = (uint32_t)((1ull << k) - 1);
+    const uint32_t s_p = host_jump(*ht, k, 1u, first_bit);
+    const uint32_t s_pm1 = host_prbs_unstep(k, tap, s_p);
+    const uint64_t eprev = host_err_bits_at(seed, first_bit - 64, err_m);
+    det->bit_in = (s_p & 1u) ^ (uint32_t)(eprev >> 63);
+    det->prbs = s_pm1;
+    det->err_sr = (uint32_t)host_brev64(eprev << 1) & mask;
+    det->reload_ctr = 0;
+    return BBB_OK;
+}
+
+int bbb_prbs_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, uint32_t err_m, uint64_t seed,
+                    bbb_det_state *det, bbb_det_counters *ctr)
+{
+    int rc = check_prbs_args(c, k, 0);
+    if (rc) return rc;
+    if (!ctr) return c->fail(BBB_EINVAL, "ctr is null");
+    if (err_m > 16) return c->fail(BBB_EINVAL, "err_m must be 0..16");
+    if (nbits >> 62) return c->fail(BBB_EINVAL, "nbits too large");
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    const PrbsTables *ht, *dt;
+    rc = get_tables(c, k, &ht, &dt);
+    if (rc) return rc;
+    c->begin_call();
+    c->last_kernel = "prbs_detect";
+    c->last_rounds = 0;
+    if (!nbits) { c->end_call(); return BBB_OK; }
+    const uint32_t tap = bbb_prbs_tap(k), mask = (uint32_t)((1ull << k) - 1);
+    DetectParams p;
+    p.tab = dt;
+    p.s_m1 = host_prbs_unstep(k, tap, host_jump(*ht, k, 1u, first_bit));
+    p.err_m = err_m;
+    p.seed = seed;
+    p.first_bit = first_bit;
+    p.nbits = nbits;
+    const uint64_t nwords = (nbits + 63) / 64;
+    uint64_t cw = (nwords + (uint64_t)c->sm_count * 1024 - 1) / ((uint64_t)c->sm_count * 1024);
+    if (cw < 32) cw = 32;
+    if (cw > 2048) cw = 2048;
+    if (c->tune_prbs_chunk_words) cw = c->tune_prbs_chunk_words;
+    uint64_t nchunks = (nwords + cw - 1) / cw;
+    while (nchunks > 0x7fffff00ull) { cw *= 2; nchunks = (nwords + cw - 1) / cw; }
+    p.chunk_words = (uint32_t)cw;
+    p.nchunks = (uint32_t)nchunks;
+    if (det) p.det0 = make_uint4(det->bit_in & 1u, det->prbs & mask, det->err_sr & mask, det->reload_ctr);
+    else p.det0 = make_uint4(0u, 1u, mask, 0u);   // reset values, prbs.py:62,80,90
+    // scratch: start_used | end[2] | ctr[5] | out[9] | changed
+    const size_t n = p.nchunks;
+    const size_t bytes = n * 16 * 3 + n * 8 * 5 + 9 * 8 + 16;
+    char *d = (char *)c->scratch(5, bytes);
+    if (!d) return BBB_ECUDA;
+    p.start_used = (uint4 *)d;
+    uint4 *end0 = (uint4 *)(d + n * 16), *end1 = (uint4 *)(d + n * 32);
+    p.ctr = (unsigned long long *)(d + n * 48);
+    unsigned long long *d_out = p.ctr + n * 5;
+    p.changed = (uint32_t *)(d_out + 9);
+    const uint32_t blocks = (p.nchunks + 127) / 128;
+    uint32_t round = 0;
+    for (;;) {
+        p.round = round;
+        p.end_prev = (round & 1) ? end0 : end1;
+        p.end_cur = (round & 1) ? end1 : end0;
+        BBB_CUDA(c, cudaMemsetAsync(p.changed, 0, 4, c->stream));
+#define PRBS_CASE(K, TAP) case K: prbs_detect_kernel<K, TAP><<<blocks, 128, 0, c->stream>>>(p); break
+        switch (k) {
+            PRBS_CASE(7, 6); PRBS_CASE(9, 5); PRBS_CASE(11, 9); PRBS_CASE(15, 14);
+            PRBS_CASE(20, 3); PRBS_CASE(23, 18); PRBS_CASE(31, 28);
+        default: return c->fail(BBB_EINVAL, "bad k");
+        }
+#undef PRBS_CASE
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        round++;
+        if (round == 1) {
+            if (p.nchunks == 1) break;
+            continue;   // round 1 checks every chunk's guess against its predecessor
+        }
+        uint32_t changed = 0;
+        BBB_CUDA(c, c->d2h(&changed, p.changed, 4));
+        BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (!changed) break;
+        if (round > p.nchunks + 1) return c->fail(BBB_ESTATE, "detector fix-up did not converge");
+    }
+    c->last_rounds = round;
+    prbs_detect_reduce_kernel<<<5, 256, 0, c->stream>>>(p.ctr, p.end_cur, p.nchunks, d_out);
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    c->end_call();
+    unsigned long long out[9];
+    BBB_CUDA(c, c->d2h(out, d_out, sizeof out));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    ctr->err += out[0];
+    ctr->err_valid += out[1];
+    ctr->reload_events += out[2];
+    ctr->reload_cycles += out[3];
+    ctr->injected += out[4];
+    if (det) {
+        det->bit_in = (uint32_t)out[5];
+        det->prbs = (uint32_t)out[6];
+        det->err_sr = (uint32_t)out[7];
+        det->reload_ctr = (uint32_t)out[8];
+    }
+    return BBB_OK;
+}
+
+}  // extern "C"

@@ -77,6 +77,8 @@ SIGNATURES = {
                                       C.c_void_p]),
     "bbb_prbs_detect": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32,
                                   C.c_uint64, _P(DetState), _P(DetCounters)]),
+    "bbb_prbs_spec_state": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, _P(DetState)]),
+    "bbb_last_rounds": (C.c_uint32, [_ctx]),
     "bbb_rnghunt_eval": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, _u64p, _u8p, _u64p]),
     "bbb_rnghunt_candidate": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, _u64p]),
     "bbb_rnghunt_sweep": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64,
@@ -286,6 +288,15 @@ class Context:
                                             C.byref(det) if det is not None else None,
                                             C.byref(ctr)))
         return ctr.as_dict()
+
+    def prbs_spec_state(self, k, first_bit, m=0, seed=1):
+        det = DetState()
+        self._check(self._L.bbb_prbs_spec_state(self._h, k, first_bit, m, seed, C.byref(det)))
+        return det
+
+    @property
+    def last_rounds(self):
+        return int(self._L.bbb_last_rounds(self._h))
 
     # ---- rnghunt ---------------------------------------------------------------------------
     def rnghunt_eval(self, n, matrices, want_poly=False):

@@ -80,8 +80,11 @@ int  bbb_sync(bbb_ctx *ctx);
  * operators, seeds, results): what bench.py reports as h2d/d2h bytes per step. */
 uint64_t bbb_last_h2d_bytes(const bbb_ctx *ctx);
 uint64_t bbb_last_d2h_bytes(const bbb_ctx *ctx);
+/* Kernel rounds the last bbb_prbs_detect needed (1 = every chunk's start state was right). */
+uint32_t bbb_last_rounds(const bbb_ctx *ctx);
 /* Tuning knobs, for tests and experiments (results never depend on them):
- *   "clt_no_spec" (0/1), "clt_spec_min_steps", "clt_spec_max_blocks". */
+ *   "clt_no_spec" (0/1), "clt_spec_min_steps", "clt_spec_max_blocks",
+ *   "prbs_chunk_words", "prbs_stream_reps". */
 int  bbb_set_tuning(bbb_ctx *ctx, const char *key, int64_t value);
 /* Region timer: CUDA events on the ctx's stream around any number of calls.
  * bbb_timer_stop waits for the stream and returns the device time in ms. */
@@ -162,6 +165,12 @@ typedef struct {
  * are ADDED to *ctr. */
 int bbb_prbs_detect(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits, uint32_t err_m,
                     uint64_t seed, bbb_det_state *det, bbb_det_counters *ctr);
+/* The state a locked detector with no reload pending has just before bit first_bit (>= 64) of that
+ * channel: what a shard that does not start at bit 0 passes as `det` before it has its left
+ * neighbour's end state; the caller compares the two and re-runs the shard on a mismatch
+ * (basebandboard_b200/sharding.py).  Pure host arithmetic. */
+int bbb_prbs_spec_state(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint32_t err_m, uint64_t seed,
+                        bbb_det_state *det);
 
 /* ---- rnghunt (software/rnghunt/src) ------------------------------------- */
 /* The body of the worker loop, rnghunt.rs:27-44, on `ncand` caller-supplied

@@ -1,0 +1,186 @@
+"""GPU parity: PRBS generator and PRBSErrorDetector through the C ABI vs the CPU oracle (bit-exact).
+
+Reference behaviour: gateware/bbb/prbs.py:14 (TAPS), :23-35 (PRBS; model :112-113), :43-99
+(PRBSErrorDetector; test protocol :124-165).  The oracle is pinned to those model lines and to the
+reference's detector property by tests/test_oracle_gen.py."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ALL_K = [7, 9, 11, 15, 20, 23, 31]
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from basebandboard_b200 import lib
+    c = lib.Context(0)
+    yield c
+    c.close()
+
+
+def _bits_to_str(words, nbits):
+    return "".join(str((int(words[i >> 6]) >> (i & 63)) & 1) for i in range(nbits))
+
+
+@pytest.mark.parametrize("k", ALL_K)
+def test_stream_golden_prefix(ctx, golden, k):
+    """The reference model's own first bits (tests/golden/golden.json, prbs.py:112-113)."""
+    want = golden["prbs"][str(k)]
+    got = ctx.prbs_stream(k, 64 * ((len(want) + 63) // 64))
+    assert _bits_to_str(got, len(want)) == want
+
+
+@pytest.mark.parametrize("k", ALL_K)
+@pytest.mark.parametrize("nbits", [0, 64, 128, 64 * 63, 64 * 64 * 31 + 64, 1 << 20])
+def test_stream_matches_oracle(ctx, orc, k, nbits):
+    got = ctx.prbs_stream(k, nbits)
+    want, _ = orc.prbs_bits(k, nbits)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("k", [7, 15, 23, 31])
+def test_stream_offsets_and_states(ctx, orc, k):
+    """Arbitrary (not word-aligned) first_bit, non-reset state0, forced multi-warp geometry."""
+    base, _ = orc.prbs_bits(k, 1 << 18, state=5)
+    for first in (1, 63, 64, 1000, 65537):
+        ctx.set_tuning("prbs_stream_reps", 1)
+        got = ctx.prbs_stream(k, 1 << 16, state0=5, first_bit=first)
+        ctx.set_tuning("prbs_stream_reps", 0)
+        want = np.zeros(1 << 10, dtype=np.uint64)
+        for i in range(1 << 10):   # re-pack the oracle's bits at the shifted offset
+            a = first + 64 * i
+            lo = int(base[a >> 6]) >> (a & 63)
+            hi = (int(base[(a >> 6) + 1]) << (64 - (a & 63))) if (a & 63) else 0
+            want[i] = (lo | hi) & 0xFFFFFFFFFFFFFFFF
+        assert np.array_equal(got, want)
+
+
+def test_stream_unaligned_device_pointer(ctx, orc):
+    """An 8-byte aligned output pointer takes the 64-bit-store kernel; same bits."""
+    import torch
+    buf = torch.zeros(4096 + 1, dtype=torch.int64, device="cuda")
+    ctx.prbs_stream_dev(31, 4096 * 64, buf.data_ptr() + 8)
+    ctx.sync()
+    want, _ = orc.prbs_bits(31, 4096 * 64)
+    assert np.array_equal(buf[1:].cpu().numpy().view(np.uint64), want)
+    assert int(buf[0]) == 0
+
+
+def test_stream_large_window_properties(ctx):
+    """2^33 bits (1 GiB) of PRBS-31 on the device: every word obeys W[j] = W[j-31] ^ W[j-28]
+    and the stream continues exactly where a second call starts."""
+    import torch
+    nw = 1 << 27
+    buf = torch.zeros(nw, dtype=torch.int64, device="cuda")
+    ctx.prbs_stream_dev(31, nw * 64, buf.data_ptr())
+    ctx.sync()
+    assert bool(torch.equal(buf[31:], buf[:-31] ^ buf[3:-28]))
+    tail = torch.zeros(1024, dtype=torch.int64, device="cuda")
+    ctx.prbs_stream_dev(31, 1024 * 64, tail.data_ptr(), first_bit=(nw - 1024) * 64)
+    ctx.sync()
+    assert bool(torch.equal(tail, buf[-1024:]))
+    # balance of an m-sequence window: ones within 0.01 % of half
+    ones = int(torch.sum(torch.bitwise_count(buf[: 1 << 20]) if hasattr(torch, "bitwise_count") else 0))
+    if ones:
+        assert abs(ones / (64 << 20) - 0.5) < 1e-3
+
+
+# ------------------------------------------------------------------------------------------------
+# detector
+# ------------------------------------------------------------------------------------------------
+def _same_det(a, b):
+    return (a.bit_in, a.prbs, a.err_sr, a.reload_ctr) == (b.bit_in, b.prbs, b.err_sr, b.reload_ctr)
+
+
+@pytest.mark.parametrize("k", ALL_K)
+@pytest.mark.parametrize("m", [0, 10, 6, 3, 1])
+def test_detect_counters_match_oracle(ctx, orc, k, m):
+    from basebandboard_b200 import lib
+    nbits = 1 << 18
+    want, _, wdet = orc.prbs_detect(k, nbits, m=m, seed=1)
+    for chunk in (0, 32, 1000):
+        ctx.set_tuning("prbs_chunk_words", chunk)
+        det = lib.DetState(0, 1, (1 << k) - 1, 0)
+        got = ctx.prbs_detect(k, nbits, m=m, seed=1, det=det)
+        assert got == want, (k, m, chunk)
+        assert _same_det(det, wdet)
+    ctx.set_tuning("prbs_chunk_words", 0)
+
+
+def test_detect_no_errors_is_startup_transient_only(ctx, orc):
+    for k in ALL_K:
+        got = ctx.prbs_detect(k, 1 << 20, m=0)
+        want, _, _ = orc.prbs_detect(k, 1 << 20, m=0)
+        assert got == want
+        assert got["reload_events"] == 1 and got["injected"] == 0   # prbs.py:80,91-94
+
+
+@pytest.mark.parametrize("nbits", [1, 63, 65, 1000, 64 * 32 + 1, 100003])
+def test_detect_ragged_lengths(ctx, orc, nbits):
+    for k in (7, 31):
+        got = ctx.prbs_detect(k, nbits, m=4, seed=9)
+        want, _, _ = orc.prbs_detect(k, nbits, m=4, seed=9)
+        assert got == want
+
+
+def test_detect_resume_and_offsets(ctx, orc):
+    """Splitting a run at arbitrary bit positions and carrying `det` gives the one-shot result."""
+    from basebandboard_b200 import lib
+    k, m, seed = 15, 5, 3
+    want, _, wdet = orc.prbs_detect(k, 300001, m=m, seed=seed)
+    det = lib.DetState(0, 1, (1 << k) - 1, 0)
+    total = {}
+    first = 0
+    for n in (1, 777, 64, 100000, 199159):
+        got = ctx.prbs_detect(k, n, m=m, seed=seed, first_bit=first, det=det)
+        for key, v in got.items():
+            total[key] = total.get(key, 0) + v
+        first += n
+    assert first == 300001 and total == want and _same_det(det, wdet)
+
+
+def test_detect_speculation_rounds(ctx, orc):
+    """Low error rate: the locked-state guess is right everywhere (2 rounds = run + check).  Heavy
+    error rate: chunks are re-run until the fixed point; the answer is still the oracle's."""
+    ctx.set_tuning("prbs_chunk_words", 32)
+    got = ctx.prbs_detect(31, 1 << 20, m=10, seed=1)
+    assert ctx.last_rounds == 2
+    assert got == orc.prbs_detect(31, 1 << 20, m=10, seed=1)[0]
+    got = ctx.prbs_detect(7, 1 << 20, m=2, seed=1)
+    assert ctx.last_rounds >= 2
+    assert got == orc.prbs_detect(7, 1 << 20, m=2, seed=1)[0]
+    ctx.set_tuning("prbs_chunk_words", 0)
+
+
+def test_spec_state_is_the_locked_state(ctx, orc):
+    """bbb_prbs_spec_state == the oracle's detector state after running from reset (no reload pending)."""
+    for k in (7, 23, 31):
+        for first in (4096, 100000, 123457):
+            _, _, det = orc.prbs_detect(k, first, m=10, seed=1)
+            if det.reload_ctr == 0:
+                assert _same_det(ctx.prbs_spec_state(k, first, m=10, seed=1), det)
+
+
+def test_detect_reference_property(ctx):
+    """prbs.py:155-163: wherever the detector is not reloading, detected errors == injected errors.
+    With p = 2^-10 and k = 31 no reload fires after start-up, so err_valid counts every injected
+    error that arrived after the start-up reload window (k + k//2 cycles, + the 1-cycle input register)."""
+    nbits = 1 << 24
+    got = ctx.prbs_detect(31, nbits, m=10, seed=1)
+    assert got["reload_events"] == 1
+    assert got["reload_cycles"] == 31 + 15
+    early = ctx.prbs_detect(31, 31 + 15 + 1, m=10, seed=1)
+    assert got["err_valid"] == got["injected"] - early["injected"] + early["err_valid"]
+
+
+def test_bad_arguments(ctx):
+    from basebandboard_b200 import lib
+    with pytest.raises(lib.BBBError):
+        ctx.prbs_stream(8, 64)
+    with pytest.raises(lib.BBBError):
+        ctx.prbs_stream(7, 100)
+    with pytest.raises(lib.BBBError):
+        ctx.prbs_stream(7, 64, state0=1 << 7)
+    with pytest.raises(lib.BBBError):
+        ctx.prbs_detect(7, 64, m=17)
