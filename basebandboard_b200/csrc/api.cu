@@ -201,6 +201,7 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
     else if (!strcmp(key, "clt_spec_min_steps")) c->tune_spec_min_steps = value < 1 ? 1u : (uint32_t)value;
     else if (!strcmp(key, "clt_spec_max_blocks")) c->tune_spec_max_blocks = value < 0 ? 0u : (uint32_t)value;
     else if (!strcmp(key, "prbs_chunk_words")) c->tune_prbs_chunk_words = value < 0 ? 0u : (uint32_t)value;
+    else if (!strcmp(key, "hunt_batch")) c->tune_hunt_batch = value < 0 ? 0u : (uint32_t)value;
     else if (!strcmp(key, "prbs_stream_reps")) c->tune_prbs_stream_reps = value < 0 ? 0u : (uint32_t)value;
     else return c->fail(BBB_EINVAL, "unknown tuning key %s", key);
     return BBB_OK;

@@ -54,6 +54,7 @@ struct bbb_ctx {
     uint32_t tune_spec_max_blocks = 0;  // 0: one CTA per SM
     uint32_t tune_prbs_chunk_words = 0; // 0: automatic detector chunk length (64-bit words)
     uint32_t tune_prbs_stream_reps = 0; // 0: automatic stream-kernel repetitions per warp
+    uint32_t tune_hunt_batch = 0;       // 0: 2^20 candidates per rnghunt batch
     uint32_t last_rounds = 0;           // kernel rounds of the last bbb_prbs_detect
     // PRBS jump tables per k (prbs.cu), built on first use
     void *prbs_host[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

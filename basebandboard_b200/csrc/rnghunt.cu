@@ -1,0 +1,736 @@
+// rnghunt.cu -- the rnghunt worker loop (software/rnghunt/src/bin/rnghunt.rs:23-57) on the device.
+//
+// Per candidate: BinaryMatrix::random (binary_matrix.rs:81-101) -> recur 2n steps from the all-ones
+// vector (rnghunt.rs:28-29, binary_matrix.rs:68-76) -> Berlekamp-Massey of the (reversed) output
+// sequence (rnghunt.rs:31-36, berlekamp_massey.rs:5-31) -> degree == n (rnghunt.rs:39-41) ->
+// is_primitive (binary_polynomial.rs:178-212).
+//
+// Device pipeline (DESIGN.md "rnghunt path"):
+//   1. hunt_front_kernel, one THREAD per candidate: generates the matrix as 4 tap slots per row
+//      (row weights are 3 or 4, rnghunt.rs:25) with the greedy column balancing done on bit masks
+//      in registers; the recurrence state lives in shared memory as one byte per state bit
+//      (word [bit][thread], the 4 bytes of a word are 4 successive generations, so a gather is one
+//      conflict-free LDS.U8); every step's output bit feeds an online Berlekamp-Massey, so the 2n
+//      sequence bits are never stored.  Candidates of degree n with constant term 1 and an odd
+//      number of terms are appended to a survivor list (stream compaction by atomic counter).
+//   2. hunt_check_kernel, one thread per (survivor, exponent): x^e mod p by square-and-multiply-by-x;
+//      first e = 2^n - 1 for every survivor, then the cofactors (2^n-1)/q for those that passed.
+//   3. hunt_classify_kernel: stage per candidate, accepted candidates appended to the hit list.
+// The Berlekamp-Massey polynomial of a sequence of length 2n with linear complexity <= n is unique,
+// so the online formulation returns exactly the reference's polynomial (parity-tested through
+// bbb_rnghunt_eval's poly_words).
+#include <algorithm>
+
+#include "bbb_internal.h"
+#include "mersenne_factors.inc"
+
+#define HUNT_PENDING 0xFFu
+
+// ---------------------------------------------------------------------------
+// candidate stream (DESIGN.md "rnghunt determinism"): draw #i of candidate (seed, c)
+// ---------------------------------------------------------------------------
+__host__ __device__ __forceinline__ uint64_t hunt_mix64(uint64_t z)
+{
+    z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull;
+    z ^= z >> 27; z *= 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return z;
+}
+
+struct HuntRng {
+    uint64_t base, i;
+    __device__ __forceinline__ void init(uint64_t seed, uint64_t c)
+    {
+        base = hunt_mix64(seed * 0x9E3779B97F4A7C15ull + c);
+        i = 0;
+    }
+    // uniform-ish index in [0, m)
+    __device__ __forceinline__ uint32_t draw(uint32_t m)
+    {
+        i += 1;
+        const uint64_t z = hunt_mix64(base + i * 0x9E3779B97F4A7C15ull);
+        return (uint32_t)(((z >> 32) * (uint64_t)m) >> 32);
+    }
+};
+
+// position of the (r+1)-th set bit of w (r < popc(w))
+__device__ __forceinline__ uint32_t nth_set_bit(uint32_t w, uint32_t r)
+{
+    uint32_t pos = 0;
+#pragma unroll
+    for (int s = 16; s; s >>= 1) {
+        const uint32_t lo = w & ((1u << s) - 1u);
+        const uint32_t pc = __popc(lo);
+        if (r >= pc) { r -= pc; w >>= s; pos += s; }
+        else w = lo;
+    }
+    return pos;
+}
+
+// BinaryMatrix::random(n, n, [3,4,4,4,4,4,4,4]) as tap lists.  All column weights are either the
+// current minimum or minimum + 1 (picks only ever raise a minimum-weight column), so the greedy rule
+// "uniform among the minimum-weight columns not yet used in this row" (binary_matrix.rs:88-94) runs
+// on three bit masks.  put(row, slot, col) receives the picks; slot 3 of a weight-3 row gets `n`.
+template <int NW, typename Put>
+__device__ __forceinline__ void hunt_generate(uint32_t n, uint64_t seed, uint64_t cand, Put put)
+{
+    HuntRng rng;
+    rng.init(seed, cand);
+    uint32_t minm[NW], nextm[NW], rowm[NW];
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+        const uint32_t lo = (uint32_t)w * 32u;
+        minm[w] = n >= lo + 32 ? 0xffffffffu : (n > lo ? (1u << (n - lo)) - 1u : 0u);
+        nextm[w] = 0;
+    }
+    for (uint32_t row = 0; row < n; row++) {
+        const uint32_t weight = rng.draw(8) == 0 ? 3u : 4u;   // rowweights[..] = [3,4,4,4,4,4,4,4]
+#pragma unroll
+        for (int w = 0; w < NW; w++) rowm[w] = 0;
+        for (uint32_t k = 0; k < 4; k++) {
+            if (k >= weight) { put(row, k, n); continue; }
+            uint32_t total = 0;
+#pragma unroll
+            for (int w = 0; w < NW; w++) total += __popc(minm[w] & ~rowm[w]);
+            if (total == 0) { put(row, k, n); continue; }   // the reference would panic (:93 unwrap)
+            uint32_t r = rng.draw(total);
+            uint32_t word = 0, wi = 0;
+            bool found = false;
+#pragma unroll
+            for (int w = 0; w < NW; w++) {
+                const uint32_t cw = minm[w] & ~rowm[w];
+                const uint32_t pc = __popc(cw);
+                if (!found) {
+                    if (r < pc) { found = true; word = cw; wi = (uint32_t)w; }
+                    else r -= pc;
+                }
+            }
+            const uint32_t bit = nth_set_bit(word, r);
+            const uint32_t m = 1u << bit;
+            put(row, k, wi * 32u + bit);
+            uint32_t any = 0;
+#pragma unroll
+            for (int w = 0; w < NW; w++) {
+                const uint32_t mm = (uint32_t)w == wi ? m : 0u;
+                minm[w] &= ~mm;
+                nextm[w] |= mm;
+                rowm[w] |= mm;
+                any |= minm[w];
+            }
+            if (!any) {
+#pragma unroll
+                for (int w = 0; w < NW; w++) { minm[w] = nextm[w]; nextm[w] = 0; }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// online Berlekamp-Massey over GF(2) (berlekamp_massey.rs:5-31 fed u[t] = recur output t)
+//   c, b: connection polynomials, bit j = coefficient c_j (LSB-first words); bsh = b * x^(t-m)
+//   win: bit j = u[t-j]
+// NWP = ceil((n+1)/32): a sequence produced by an n-dimensional recurrence has complexity <= n.
+// ---------------------------------------------------------------------------
+template <int NWP>
+struct HuntBM {
+    uint32_t c[NWP], bsh[NWP], win[NWP];
+    uint32_t l, t;
+    __device__ __forceinline__ void init()
+    {
+#pragma unroll
+        for (int w = 0; w < NWP; w++) { c[w] = 0; bsh[w] = 0; win[w] = 0; }
+        c[0] = 1;
+        bsh[0] = 1;
+        l = 0;
+        t = 0;
+    }
+    __device__ __forceinline__ void push(uint32_t bit)
+    {
+        // slide the window and b * x^(t-m) by one position
+#pragma unroll
+        for (int w = NWP - 1; w > 0; w--) {
+            win[w] = (win[w] << 1) | (win[w - 1] >> 31);
+            bsh[w] = (bsh[w] << 1) | (bsh[w - 1] >> 31);
+        }
+        win[0] = (win[0] << 1) | (bit & 1u);
+        bsh[0] <<= 1;
+        uint32_t d = 0;
+#pragma unroll
+        for (int w = 0; w < NWP; w++) d ^= c[w] & win[w];
+        if (__popc(d) & 1) {                                   // discrepancy (:17)
+            const bool grow = 2 * l <= t;                      // l <= n/2 (:23)
+#pragma unroll
+            for (int w = 0; w < NWP; w++) {
+                const uint32_t tc = c[w];
+                c[w] ^= bsh[w];                                // c ^= b >> (n - m) (:21-22)
+                if (grow) bsh[w] = tc;
+            }
+            if (grow) l = t + 1 - l;
+        }
+        t++;
+    }
+};
+
+// ---------------------------------------------------------------------------
+// outputs of the front kernels
+// ---------------------------------------------------------------------------
+struct HuntOut {
+    uint8_t *stage;            // [count] BBB_STAGE_DEGREE / _FILTER / HUNT_PENDING
+    uint32_t *surv_count;      // survivors appended so far
+    uint32_t *surv_cand;       // [cap] candidate slot (index into stage[])
+    uint32_t *surv_poly;       // [cap][NWP] p(x), bit i = coefficient of x^i
+    uint64_t *poly_out;        // [count][ceil((n+1)/64)] reference layout, or null
+};
+
+// Degree / filter verdict of one candidate and, for survivors, its polynomial.
+// c: connection polynomial bits c_j (the reference's coefficient j, highest power first).
+template <int NWP>
+__device__ __noinline__ void hunt_finish(const HuntOut &o, uint32_t n, uint32_t slot, const uint32_t (&creg)[NWP],
+                                         uint32_t l)
+{
+    const uint32_t pw64 = (n + 1 + 63) / 64;
+    uint32_t c[NWP];   // a copy the dynamic indexing below may spill without touching the caller's registers
+#pragma unroll
+    for (int w = 0; w < NWP; w++) c[w] = creg[w];
+    if (o.poly_out) {
+        // BinaryPolynomial words: coefficient j at word j/64, bit 63 - j%64 (binary_vector.rs:25-31)
+        for (uint32_t w = 0; w < pw64; w++) {
+            uint64_t v = 0;
+            if (l == n) {
+                const uint32_t lo = 2 * w < (uint32_t)NWP ? c[2 * w] : 0u;
+                const uint32_t hi = 2 * w + 1 < (uint32_t)NWP ? c[2 * w + 1] : 0u;
+                v = __brevll(((uint64_t)hi << 32) | lo);
+            }
+            o.poly_out[(size_t)slot * pw64 + w] = v;
+        }
+    }
+    if (l != n) { o.stage[slot] = BBB_STAGE_DEGREE; return; }               // rnghunt.rs:39-41
+    uint32_t ones = 0;
+#pragma unroll
+    for (int w = 0; w < NWP; w++) ones += __popc(c[w]);
+    const uint32_t cn = (c[n >> 5] >> (n & 31)) & 1u;                       // constant term = c_n
+    if (!cn || !(ones & 1u)) { o.stage[slot] = BBB_STAGE_FILTER; return; }  // binary_polynomial.rs:185-192
+    o.stage[slot] = HUNT_PENDING;
+    const uint32_t s = atomicAdd(o.surv_count, 1u);
+    o.surv_cand[s] = slot;
+    // p(x) = sum c_j x^(n-j): reverse the n+1 coefficient bits
+    uint32_t *dst = o.surv_poly + (size_t)s * NWP;
+    for (int w = 0; w < NWP; w++) dst[w] = 0;
+    for (uint32_t j = 0; j <= n; j++) {
+        const uint32_t b = (c[j >> 5] >> (j & 31)) & 1u;
+        const uint32_t i = n - j;
+        dst[i >> 5] |= b << (i & 31);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// front kernel for generated candidates: one thread per candidate
+// ---------------------------------------------------------------------------
+struct FrontParams {
+    uint32_t n;
+    uint64_t seed, first, stride;
+    uint32_t count;
+    HuntOut out;
+    uint16_t *dump_taps;   // [n][4] taps of candidate `first` (bbb_rnghunt_candidate), else null
+};
+
+// shared memory: state bytes xs[(n+1)][B] words, then taps[n][B] (4 x TapT per thread and row)
+template <int NW, typename TapT>
+__global__ void hunt_front_kernel(FrontParams p)
+{
+    constexpr int NWP = NW + 1;   // n + 1 bits always fit
+    extern __shared__ uint32_t hsm[];
+    const uint32_t B = blockDim.x, tid = threadIdx.x, n = p.n;
+    const uint32_t slot = blockIdx.x * B + tid;
+    uint32_t *xs = hsm;                                   // word (bit, thread): 4 generations
+    TapT *taps = (TapT *)(hsm + (size_t)(n + 1) * B);     // [row][thread][4]
+    if (slot >= p.count) return;
+    const uint64_t cand = p.first + (uint64_t)slot * p.stride;
+
+    hunt_generate<NW>(n, p.seed, cand, [&](uint32_t row, uint32_t k, uint32_t col) {
+        taps[((size_t)row * B + tid) * 4 + k] = (TapT)col;
+        if (p.dump_taps && slot == 0) p.dump_taps[row * 4 + k] = (uint16_t)(col == n ? 0xFFFFu : col);
+    });
+    if (p.dump_taps) return;
+
+    // b = all ones (rnghunt.rs:28): generation 0; the extra row n stays 0 (empty tap slots)
+    for (uint32_t i = 0; i < n; i++) xs[i * B + tid] = 1u;
+    xs[n * B + tid] = 0u;
+
+    HuntBM<NWP> bm;
+    bm.init();
+    const uint8_t *xb = (const uint8_t *)(xs + tid);      // byte (bit i, generation g) at xb[i*4B + g]
+    uint8_t *xw = (uint8_t *)(xs + tid);
+    const uint32_t rs = 4 * B;                            // byte stride between state bits
+    for (uint32_t step = 0; step < 2 * n; step++) {
+        const uint32_t go = step & 3, gn = (step + 1) & 3;
+        // x' = A . x (binary_matrix.rs:53-64 / :72): row r gathers its 3-4 taps
+#pragma unroll 4
+        for (uint32_t r = 0; r < n; r++) {
+            uint32_t v;
+            if (sizeof(TapT) == 1) {
+                const uint32_t t4 = *(const uint32_t *)(taps + ((size_t)r * B + tid) * 4);
+                v = xb[(t4 & 0xffu) * rs + go] ^ xb[((t4 >> 8) & 0xffu) * rs + go] ^
+                    xb[((t4 >> 16) & 0xffu) * rs + go] ^ xb[(t4 >> 24) * rs + go];
+            } else {
+                const uint2 t4 = *(const uint2 *)(taps + ((size_t)r * B + tid) * 4);
+                v = xb[(t4.x & 0xffffu) * rs + go] ^ xb[(t4.x >> 16) * rs + go] ^
+                    xb[(t4.y & 0xffffu) * rs + go] ^ xb[(t4.y >> 16) * rs + go];
+            }
+            xw[r * rs + gn] = (uint8_t)v;
+        }
+        bm.push(xb[gn]);                                  // x[0] after the step (binary_matrix.rs:73)
+    }
+    hunt_finish<NWP>(p.out, n, slot, bm.c, bm.l);
+}
+
+// ---------------------------------------------------------------------------
+// front kernel for caller-supplied dense matrices (bbb_rnghunt_eval): one thread per matrix,
+// BinaryMatrix layout (binary_matrix.rs:15-19), dot() as the XOR of the selected columns (:53-64)
+// ---------------------------------------------------------------------------
+template <int NW64>
+__global__ void __launch_bounds__(64)
+hunt_front_dense_kernel(uint32_t n, uint32_t count, const uint64_t *__restrict__ mats, HuntOut out)
+{
+    constexpr int NWP = (NW64 * 64 + 1 + 31) / 32;
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= count) return;
+    const uint64_t *m = mats + (size_t)slot * n * NW64;
+    uint64_t x[NW64];
+#pragma unroll
+    for (int w = 0; w < NW64; w++) {   // BinaryVector::from_bits(all ones): bit i at word i/64, bit 63 - i%64
+        const uint32_t lo = (uint32_t)w * 64u;
+        x[w] = n >= lo + 64 ? ~0ull : (n > lo ? ~0ull << (64 - (n - lo)) : 0ull);
+    }
+    HuntBM<NWP> bm;
+    bm.init();
+    for (uint32_t step = 0; step < 2 * n; step++) {
+        uint64_t y[NW64];
+#pragma unroll
+        for (int w = 0; w < NW64; w++) y[w] = 0;
+#pragma unroll
+        for (int w = 0; w < NW64; w++) {
+            uint64_t bits = x[w];
+            while (bits) {
+                const uint32_t lz = __clzll(bits);
+                bits &= ~(0x8000000000000000ull >> lz);
+                const uint64_t *col = m + (size_t)((uint32_t)w * 64u + lz) * NW64;
+#pragma unroll
+                for (int v = 0; v < NW64; v++) y[v] ^= col[v];
+            }
+        }
+#pragma unroll
+        for (int w = 0; w < NW64; w++) x[w] = y[w];
+        bm.push((uint32_t)(x[0] >> 63));
+    }
+    hunt_finish<NWP>(out, n, slot, bm.c, bm.l);
+}
+
+// ---------------------------------------------------------------------------
+// primitivity: x^e mod p == 1 ?  (binary_polynomial.rs:136-175, check_integer)
+// polynomials LSB-first in NWP 32-bit words, deg p = n
+// ---------------------------------------------------------------------------
+template <int NWP>
+__device__ __forceinline__ void poly_mulx(uint32_t (&v)[NWP], const uint32_t (&p)[NWP], uint32_t n)
+{
+#pragma unroll
+    for (int w = NWP - 1; w > 0; w--) v[w] = (v[w] << 1) | (v[w - 1] >> 31);
+    v[0] <<= 1;
+    // bit n set -> subtract p (clears it)
+    uint32_t top = 0;
+#pragma unroll
+    for (int w = 0; w < NWP; w++) if ((uint32_t)w == (n >> 5)) top = (v[w] >> (n & 31)) & 1u;
+    const uint32_t m = 0u - top;
+#pragma unroll
+    for (int w = 0; w < NWP; w++) v[w] ^= p[w] & m;
+}
+
+// r = r * r mod p, Horner over the bits of r from the top (binary_polynomial.rs:88-133 computes the
+// same product by shift-and-add)
+template <int NWP>
+__device__ __forceinline__ void poly_square(uint32_t (&r)[NWP], const uint32_t (&p)[NWP], uint32_t n)
+{
+    uint32_t acc[NWP];
+#pragma unroll
+    for (int w = 0; w < NWP; w++) acc[w] = 0;
+#pragma unroll
+    for (int w = NWP - 1; w >= 0; w--) {
+        const uint32_t base = (uint32_t)w * 32u;
+        if (base < n) {                                   // r has degree < n
+            const uint32_t word = r[w];
+            const int hi = n - 1 - base < 31u ? (int)(n - 1 - base) : 31;
+#pragma unroll 1
+            for (int b = hi; b >= 0; b--) {
+                poly_mulx<NWP>(acc, p, n);
+                const uint32_t m = 0u - ((word >> b) & 1u);
+#pragma unroll
+                for (int v = 0; v < NWP; v++) acc[v] ^= r[v] & m;
+            }
+        }
+    }
+#pragma unroll
+    for (int w = 0; w < NWP; w++) r[w] = acc[w];
+}
+
+struct CheckParams {
+    uint32_t n, nitems, nexp;          // nexp exponents per polynomial in this launch
+    uint32_t exp_first;                // index of the first exponent (0 = 2^n-1, i >= 1 = cofactor i)
+    const uint32_t *poly_index;        // [npoly] survivor index of polynomial q, or null = identity
+    const uint32_t *polys;             // [..][NWP]
+    const uint64_t *exp_words;         // all exponents of n back to back, MS word first
+    const uint32_t *exp_off;           // [nf+1] word offsets into exp_words
+    uint32_t *result;                  // [survivor] bit (exp index) set when x^e == 1
+};
+
+template <int NWP>
+__global__ void __launch_bounds__(128)
+hunt_check_kernel(CheckParams q)
+{
+    const uint32_t item = blockIdx.x * blockDim.x + threadIdx.x;
+    if (item >= q.nitems) return;
+    const uint32_t pi = item / q.nexp, ei = q.exp_first + item % q.nexp;
+    const uint32_t sidx = q.poly_index ? q.poly_index[pi] : pi;
+    uint32_t p[NWP], r[NWP];
+#pragma unroll
+    for (int w = 0; w < NWP; w++) { p[w] = q.polys[(size_t)sidx * NWP + w]; r[w] = 0; }
+    r[0] = 1;                                              // modexp starts from 1 (:138-142)
+    const uint64_t *e = q.exp_words + q.exp_off[ei];
+    const uint32_t ew = q.exp_off[ei + 1] - q.exp_off[ei];
+    bool started = false;
+    for (uint32_t w = 0; w < ew; w++) {
+        const uint64_t word = e[w];
+        for (int b = 63; b >= 0; b--) {
+            const uint32_t bit = (uint32_t)(word >> b) & 1u;
+            if (!started) {
+                if (!bit) continue;                        // 1 squared stays 1
+                started = true;
+            } else {
+                poly_square<NWP>(r, p, q.n);
+            }
+            if (bit) poly_mulx<NWP>(r, p, q.n);
+        }
+    }
+    uint32_t rest = r[0] ^ 1u;
+#pragma unroll
+    for (int w = 1; w < NWP; w++) rest |= r[w];
+    if (rest == 0) atomicOr(&q.result[sidx], 1u << (ei > 31 ? 31 : ei));
+}
+
+// survivors whose x^(2^n-1) == 1 go on to the cofactor tests (binary_polynomial.rs:198-208)
+__global__ void hunt_compact_kernel(const uint32_t *__restrict__ result, uint32_t nsurv, uint32_t *pass_count,
+                                    uint32_t *pass_index)
+{
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nsurv) return;
+    if (result[s] & 1u) pass_index[atomicAdd(pass_count, 1u)] = s;
+}
+
+__global__ void hunt_classify_kernel(const uint32_t *__restrict__ result, const uint32_t *__restrict__ surv_cand,
+                                     uint32_t nsurv, uint8_t *stage, uint32_t *hit_count, uint32_t *hits)
+{
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= nsurv) return;
+    const uint32_t r = result[s];
+    uint8_t st;
+    if (!(r & 1u)) st = BBB_STAGE_ORDER;
+    else if (r & ~1u) st = BBB_STAGE_FACTOR;
+    else st = BBB_STAGE_PRIMITIVE;
+    const uint32_t slot = surv_cand[s];
+    stage[slot] = st;
+    if (st == BBB_STAGE_PRIMITIVE) hits[atomicAdd(hit_count, 1u)] = slot;
+}
+
+__global__ void hunt_count_kernel(const uint8_t *__restrict__ stage, uint32_t count, unsigned long long *counts)
+{
+    __shared__ uint32_t sh[BBB_NSTAGES];
+    if (threadIdx.x < BBB_NSTAGES) sh[threadIdx.x] = 0;
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const uint8_t s = stage[i];
+        if (s < BBB_NSTAGES) atomicAdd(&sh[s], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < BBB_NSTAGES && sh[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+struct HuntBuffers {
+    uint8_t *stage;
+    uint32_t *counters;            // [0] survivors, [1] order passers, [2] hits
+    unsigned long long *counts;    // [BBB_NSTAGES]
+    uint32_t *surv_cand, *surv_poly, *result, *pass_index, *hits, *exp_off;
+    uint64_t *exp_words;
+    uint32_t nf;                   // exponents for n (entry 0 = 2^n - 1)
+};
+
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+// Carves scratch slot 6 for a batch of `cap` candidates and uploads the exponent table of n
+// (factors.rs:7-16: [2^n-1, (2^n-1)/q_1, ...], MS word first).
+static int hunt_buffers(bbb_ctx *c, uint32_t n, uint32_t cap, uint32_t nwp, HuntBuffers &b)
+{
+    const uint32_t e0 = BBB_MF_OFFSETS[n - 1], e1 = BBB_MF_OFFSETS[n];
+    b.nf = e1 - e0;
+    std::vector<uint32_t> off(b.nf + 1);
+    std::vector<uint64_t> words;
+    for (uint32_t i = 0; i < b.nf; i++) {
+        off[i] = (uint32_t)words.size();
+        for (uint32_t w = BBB_MF_ENTRIES[e0 + i]; w < BBB_MF_ENTRIES[e0 + i + 1]; w++) words.push_back(BBB_MF_WORDS[w]);
+    }
+    off[b.nf] = (uint32_t)words.size();
+    size_t at = 0;
+    auto take = [&](size_t bytes) { size_t o = at; at += align256(bytes); return o; };
+    const size_t o_stage = take(cap), o_ctr = take(16), o_counts = take(8 * BBB_NSTAGES),
+                 o_cand = take((size_t)cap * 4), o_poly = take((size_t)cap * nwp * 4), o_res = take((size_t)cap * 4),
+                 o_pass = take((size_t)cap * 4), o_hits = take((size_t)cap * 4), o_eoff = take(off.size() * 4),
+                 o_ew = take(words.size() * 8);
+    char *d = (char *)c->scratch(6, at);
+    if (!d) return BBB_ECUDA;
+    b.stage = (uint8_t *)(d + o_stage);
+    b.counters = (uint32_t *)(d + o_ctr);
+    b.counts = (unsigned long long *)(d + o_counts);
+    b.surv_cand = (uint32_t *)(d + o_cand);
+    b.surv_poly = (uint32_t *)(d + o_poly);
+    b.result = (uint32_t *)(d + o_res);
+    b.pass_index = (uint32_t *)(d + o_pass);
+    b.hits = (uint32_t *)(d + o_hits);
+    b.exp_off = (uint32_t *)(d + o_eoff);
+    b.exp_words = (uint64_t *)(d + o_ew);
+    BBB_CUDA(c, c->h2d(b.exp_off, off.data(), off.size() * 4));
+    BBB_CUDA(c, c->h2d(b.exp_words, words.data(), words.size() * 8));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));   // off / words are about to go out of scope
+    return BBB_OK;
+}
+
+static int launch_check(bbb_ctx *c, uint32_t nwp, const CheckParams &q)
+{
+    if (!q.nitems) return BBB_OK;
+    const uint32_t blocks = (q.nitems + 127) / 128;
+#define CHECK_CASE(N) case N: hunt_check_kernel<N><<<blocks, 128, 0, c->stream>>>(q); break
+    switch (nwp) {
+        CHECK_CASE(2); CHECK_CASE(3); CHECK_CASE(4); CHECK_CASE(5); CHECK_CASE(6); CHECK_CASE(7); CHECK_CASE(8);
+        CHECK_CASE(9); CHECK_CASE(10); CHECK_CASE(11); CHECK_CASE(12); CHECK_CASE(13); CHECK_CASE(14);
+        CHECK_CASE(15); CHECK_CASE(16); CHECK_CASE(17);
+    default: return c->fail(BBB_EINVAL, "bad polynomial width");
+    }
+#undef CHECK_CASE
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    return BBB_OK;
+}
+
+// Stages 2 and 3 of the pipeline for the survivors the front kernel left in `b`; on return
+// b.stage holds the final verdict of every candidate of the batch, hits[] the accepted slots.
+static int hunt_back_end(bbb_ctx *c, uint32_t n, uint32_t count, uint32_t nwp, HuntBuffers &b,
+                         std::vector<uint32_t> &hit_slots)
+{
+    uint32_t ctr[3] = {0, 0, 0};
+    BBB_CUDA(c, c->d2h(ctr, b.counters, 4));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    const uint32_t nsurv = ctr[0];
+    hit_slots.clear();
+    if (nsurv) {
+        BBB_CUDA(c, cudaMemsetAsync(b.result, 0, (size_t)nsurv * 4, c->stream));
+        CheckParams q;
+        q.n = n; q.polys = b.surv_poly; q.exp_words = b.exp_words; q.exp_off = b.exp_off; q.result = b.result;
+        q.nitems = nsurv; q.nexp = 1; q.exp_first = 0; q.poly_index = nullptr;            // x^(2^n-1) == 1 ?
+        int rc = launch_check(c, nwp, q);
+        if (rc) return rc;
+        const uint32_t gb = (nsurv + 255) / 256;
+        if (b.nf > 1) {
+            hunt_compact_kernel<<<gb, 256, 0, c->stream>>>(b.result, nsurv, b.counters + 1, b.pass_index);
+            c->last_launches++;
+            BBB_CUDA(c, c->d2h(ctr + 1, b.counters + 1, 4));
+            BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+            const uint64_t items = (uint64_t)ctr[1] * (b.nf - 1);
+            if (items > 0xfffffff0ull) return c->fail(BBB_EINVAL, "batch too large");
+            q.nitems = (uint32_t)items; q.nexp = b.nf - 1; q.exp_first = 1; q.poly_index = b.pass_index;
+            rc = launch_check(c, nwp, q);                                                  // cofactors
+            if (rc) return rc;
+        }
+        hunt_classify_kernel<<<gb, 256, 0, c->stream>>>(b.result, b.surv_cand, nsurv, b.stage, b.counters + 2, b.hits);
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        BBB_CUDA(c, c->d2h(ctr + 2, b.counters + 2, 4));
+        BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (ctr[2]) {
+            hit_slots.resize(ctr[2]);
+            BBB_CUDA(c, c->d2h(hit_slots.data(), b.hits, (size_t)ctr[2] * 4));
+            BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+        }
+    }
+    hunt_count_kernel<<<c->sm_count * 2, 256, 0, c->stream>>>(b.stage, count, b.counts);
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    return BBB_OK;
+}
+
+static int launch_front(bbb_ctx *c, const FrontParams &p)
+{
+    const uint32_t n = p.n, nw = (n + 31) / 32, B = 32;
+    const bool wide = n > 255;                         // the "no tap" index n must fit the tap type
+    const size_t smem = (size_t)B * ((n + 1) * 4 + (size_t)n * 4 * (wide ? 2 : 1));
+    const uint32_t blocks = (p.count + B - 1) / B;
+#define FRONT_CASE(NW, T)                                                                              \
+    case NW:                                                                                           \
+        BBB_CUDA(c, cudaFuncSetAttribute(hunt_front_kernel<NW, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                         (int)smem));                                                  \
+        hunt_front_kernel<NW, T><<<blocks, B, smem, c->stream>>>(p);                                   \
+        break
+    if (!wide) {
+        switch (nw) {
+            FRONT_CASE(1, uint8_t); FRONT_CASE(2, uint8_t); FRONT_CASE(3, uint8_t); FRONT_CASE(4, uint8_t);
+            FRONT_CASE(5, uint8_t); FRONT_CASE(6, uint8_t); FRONT_CASE(7, uint8_t); FRONT_CASE(8, uint8_t);
+        default: return c->fail(BBB_EINVAL, "bad n");
+        }
+    } else {
+        switch (nw) {
+            FRONT_CASE(8, uint16_t); FRONT_CASE(9, uint16_t); FRONT_CASE(10, uint16_t); FRONT_CASE(11, uint16_t);
+            FRONT_CASE(12, uint16_t); FRONT_CASE(13, uint16_t); FRONT_CASE(14, uint16_t); FRONT_CASE(15, uint16_t);
+            FRONT_CASE(16, uint16_t);
+        default: return c->fail(BBB_EINVAL, "bad n");
+        }
+    }
+#undef FRONT_CASE
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    return BBB_OK;
+}
+
+static int check_hunt_n(bbb_ctx *c, uint32_t n)
+{
+    if (!c) return BBB_EINVAL;
+    if (n < 8 || n > BBB_MAX_N) return c->fail(BBB_EINVAL, "n=%u: need 8 <= n <= 512", n);
+    return BBB_OK;
+}
+
+extern "C" {
+
+int bbb_rnghunt_sweep(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uint64_t stride, uint64_t count,
+                      uint32_t k, uint64_t *best, uint32_t *nfound, uint64_t *stage_counts, uint8_t *stage_out)
+{
+    int rc = check_hunt_n(c, n);
+    if (rc) return rc;
+    if (!stride) return c->fail(BBB_EINVAL, "stride must be >= 1");
+    if (k && !best) return c->fail(BBB_EINVAL, "best is null");
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    c->begin_call();
+    c->last_kernel = "rnghunt_sweep";
+    const uint32_t nwp = (n + 31) / 32 + 1;
+    const uint64_t batch_max = c->tune_hunt_batch ? c->tune_hunt_batch : (1u << 20);
+    const uint32_t cap = (uint32_t)(count < batch_max ? (count ? count : 1) : batch_max);
+    HuntBuffers b;
+    rc = hunt_buffers(c, n, cap, nwp, b);
+    if (rc) return rc;
+    BBB_CUDA(c, cudaMemsetAsync(b.counts, 0, 8 * BBB_NSTAGES, c->stream));
+    std::vector<uint64_t> found;
+    std::vector<uint32_t> hit_slots;
+    for (uint64_t done = 0; done < count; done += cap) {
+        const uint32_t nb = (uint32_t)(count - done < cap ? count - done : cap);
+        BBB_CUDA(c, cudaMemsetAsync(b.counters, 0, 16, c->stream));
+        FrontParams p;
+        p.n = n; p.seed = seed; p.first = first + done * stride; p.stride = stride; p.count = nb;
+        p.out.stage = b.stage; p.out.surv_count = b.counters; p.out.surv_cand = b.surv_cand;
+        p.out.surv_poly = b.surv_poly; p.out.poly_out = nullptr; p.dump_taps = nullptr;
+        rc = launch_front(c, p);
+        if (rc) return rc;
+        rc = hunt_back_end(c, n, nb, nwp, b, hit_slots);
+        if (rc) return rc;
+        for (uint32_t s : hit_slots) found.push_back(p.first + (uint64_t)s * stride);
+        if (stage_out) {
+            BBB_CUDA(c, c->d2h(stage_out + done, b.stage, nb));
+            BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+        }
+    }
+    c->end_call();
+    unsigned long long counts[BBB_NSTAGES];
+    BBB_CUDA(c, c->d2h(counts, b.counts, sizeof counts));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (stage_counts) for (int i = 0; i < BBB_NSTAGES; i++) stage_counts[i] += counts[i];
+    std::sort(found.begin(), found.end());
+    uint32_t nf = (uint32_t)(found.size() < k ? found.size() : k);
+    for (uint32_t i = 0; i < nf; i++) best[i] = found[i];
+    if (nfound) *nfound = nf;
+    return BBB_OK;
+}
+
+int bbb_rnghunt_candidate(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t cand, uint64_t *matrix_words)
+{
+    int rc = check_hunt_n(c, n);
+    if (rc) return rc;
+    if (!matrix_words) return c->fail(BBB_EINVAL, "matrix_words is null");
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    c->begin_call();
+    c->last_kernel = "rnghunt_candidate";
+    uint16_t *d_taps = (uint16_t *)c->scratch(5, (size_t)n * 4 * 2);
+    if (!d_taps) return BBB_ECUDA;
+    FrontParams p;
+    memset(&p, 0, sizeof p);
+    p.n = n; p.seed = seed; p.first = cand; p.stride = 1; p.count = 1; p.dump_taps = d_taps;
+    rc = launch_front(c, p);
+    if (rc) return rc;
+    c->end_call();
+    std::vector<uint16_t> taps((size_t)n * 4);
+    BBB_CUDA(c, c->d2h(taps.data(), d_taps, taps.size() * 2));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    const uint32_t wpc = (n + 63) / 64;
+    memset(matrix_words, 0, (size_t)n * wpc * 8);
+    for (uint32_t r = 0; r < n; r++)
+        for (uint32_t s = 0; s < 4; s++) {
+            const uint16_t col = taps[r * 4 + s];
+            if (col == 0xFFFFu) continue;
+            matrix_words[(size_t)col * wpc + r / 64] |= 1ull << (63 - r % 64);   // binary_matrix.rs:15-19
+        }
+    return BBB_OK;
+}
+
+int bbb_rnghunt_eval(bbb_ctx *c, uint32_t n, uint64_t ncand, const uint64_t *matrices, uint8_t *stage,
+                     uint64_t *poly_words)
+{
+    int rc = check_hunt_n(c, n);
+    if (rc) return rc;
+    if (!matrices || !stage) return c->fail(BBB_EINVAL, "null argument");
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    c->begin_call();
+    c->last_kernel = "rnghunt_eval";
+    const uint32_t nw64 = (n + 63) / 64, nwp = 2 * nw64 + 1, pw64 = (n + 1 + 63) / 64;
+    const size_t mat_bytes = (size_t)n * nw64 * 8;
+    const uint32_t cap = (uint32_t)(ncand < 65536 ? (ncand ? ncand : 1) : 65536);
+    HuntBuffers b;
+    rc = hunt_buffers(c, n, cap, nwp, b);
+    if (rc) return rc;
+    uint64_t *d_m = (uint64_t *)c->scratch(5, cap * mat_bytes + (size_t)cap * pw64 * 8);
+    if (!d_m) return BBB_ECUDA;
+    uint64_t *d_poly = (uint64_t *)((char *)d_m + cap * mat_bytes);
+    std::vector<uint32_t> hit_slots;
+    for (uint64_t done = 0; done < ncand; done += cap) {
+        const uint32_t nb = (uint32_t)(ncand - done < cap ? ncand - done : cap);
+        BBB_CUDA(c, cudaMemsetAsync(b.counters, 0, 16, c->stream));
+        BBB_CUDA(c, cudaMemsetAsync(b.counts, 0, 8 * BBB_NSTAGES, c->stream));
+        BBB_CUDA(c, c->h2d(d_m, matrices + done * n * nw64, nb * mat_bytes));
+        HuntOut o;
+        o.stage = b.stage; o.surv_count = b.counters; o.surv_cand = b.surv_cand; o.surv_poly = b.surv_poly;
+        o.poly_out = poly_words ? d_poly : nullptr;
+        const uint32_t blocks = (nb + 63) / 64;
+#define DENSE_CASE(N) case N: hunt_front_dense_kernel<N><<<blocks, 64, 0, c->stream>>>(n, nb, d_m, o); break
+        switch (nw64) {
+            DENSE_CASE(1); DENSE_CASE(2); DENSE_CASE(3); DENSE_CASE(4); DENSE_CASE(5); DENSE_CASE(6);
+            DENSE_CASE(7); DENSE_CASE(8);
+        default: return c->fail(BBB_EINVAL, "bad n");
+        }
+#undef DENSE_CASE
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        rc = hunt_back_end(c, n, nb, nwp, b, hit_slots);
+        if (rc) return rc;
+        BBB_CUDA(c, c->d2h(stage + done, b.stage, nb));
+        if (poly_words) BBB_CUDA(c, c->d2h(poly_words + done * pw64, d_poly, (size_t)nb * pw64 * 8));
+        BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    c->end_call();
+    return BBB_OK;
+}
+
+}  // extern "C"

@@ -80,10 +80,6 @@ def test_stream_large_window_properties(ctx):
     ctx.prbs_stream_dev(31, 1024 * 64, tail.data_ptr(), first_bit=(nw - 1024) * 64)
     ctx.sync()
     assert bool(torch.equal(tail, buf[-1024:]))
-    # balance of an m-sequence window: ones within 0.01 % of half
-    ones = int(torch.sum(torch.bitwise_count(buf[: 1 << 20]) if hasattr(torch, "bitwise_count") else 0))
-    if ones:
-        assert abs(ones / (64 << 20) - 0.5) < 1e-3
 
 
 # ------------------------------------------------------------------------------------------------
