@@ -527,16 +527,20 @@ static uint64_t host_brev64(uint64_t x)
 int bbb_prbs_spec_state(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint32_t err_m, uint64_t seed,
                         bbb_det_state *det)
 {
-    int rc = check_prbs_args(c, k, 0);
-    if (rc) return rc;
-    if (!det) return c->fail(BBB_EINVAL, "det is null");
-    if (err_m > 16) return c->fail(BBB_EINVAL, "err_m must be 0..16");
-    if (first_bit < 64) return c->fail(BBB_EINVAL, "first_bit must be >= 64 (the detector starts from reset at 0)");
-    const PrbsTables *ht, *dt;
-    rc = get_tables(c, k, &ht, &dt);
-    if (rc) return rc;
-    const uint32_t tap = bbb_prbs_tap(k), mask = (uint32_t)((1ull << k) - 1);
-    const uint32_t s_p = host_jump(*ht, k, 1u, first_bit);
+    // pure host arithmetic: works without a ctx (and without a GPU) so that shard planning can run anywhere
+    const uint32_t tap = bbb_prbs_tap(k);
+    if (!tap || !det || err_m > 16 || first_bit < 64) {
+        const char *why = !tap ? "k is not one of prbs.py:14's TAPS keys" : !det ? "det is null"
+                          : err_m > 16 ? "err_m must be 0..16"
+                          : "first_bit must be >= 64 (the detector starts from reset at 0)";
+        return c ? c->fail(BBB_EINVAL, "%s", why) : BBB_EINVAL;
+    }
+    PrbsTables *t = new (std::nothrow) PrbsTables;
+    if (!t) return BBB_ENOMEM;
+    build_tables(k, tap, *t);
+    const uint32_t mask = (uint32_t)((1ull << k) - 1);
+    const uint32_t s_p = host_jump(*t, k, 1u, first_bit);
+    delete t;
     const uint32_t s_pm1 = host_prbs_unstep(k, tap, s_p);
     const uint64_t eprev = host_err_bits_at(seed, first_bit - 64, err_m);
     det->bit_in = (s_p & 1u) ^ (uint32_t)(eprev >> 63);

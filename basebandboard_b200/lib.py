@@ -290,9 +290,7 @@ class Context:
         return ctr.as_dict()
 
     def prbs_spec_state(self, k, first_bit, m=0, seed=1):
-        det = DetState()
-        self._check(self._L.bbb_prbs_spec_state(self._h, k, first_bit, m, seed, C.byref(det)))
-        return det
+        return prbs_spec_state(k, first_bit, m, seed)
 
     @property
     def last_rounds(self):
@@ -331,6 +329,16 @@ class Context:
         if want_stages:
             res["stages"] = stages
         return res
+
+
+def prbs_spec_state(k, first_bit, m=0, seed=1):
+    """State of a locked detector just before bit `first_bit` (bbb_prbs_spec_state; host arithmetic,
+    needs no GPU)."""
+    det = DetState()
+    rc = load().bbb_prbs_spec_state(None, k, first_bit, m, seed, C.byref(det))
+    if rc != 0:
+        raise BBBError(rc, "bbb_prbs_spec_state(k=%d, first_bit=%d, m=%d)" % (k, first_bit, m))
+    return det
 
 
 def clt_stats(n, hist, model=MODEL_GATEWARE):

@@ -1,0 +1,149 @@
+"""Multi-GPU sharding of the three paths: one process per GPU, no data-path collective.
+
+Every path is cut into independent units; the only exchange is one small
+reduction / gather of results at the end (torch.distributed: NCCL on the GPU box, gloo in the CPU
+tests):
+
+  CLT-GRNG fused      rank r owns sample indices [first + r*per, ...) -> all-reduce(sum) of
+                      u64[n+3] = histogram | sum g | sum g^2
+  PRBS detect         rank r owns a contiguous bit range and starts from the locked detector state
+                      (bbb_prbs_spec_state); end states are all-gathered and a rank whose left
+                      neighbour ended in a different state re-runs its range from that state, until
+                      every rank started where its neighbour ended -> all-reduce(sum) of 5 counters
+  rnghunt sweep       rank r owns candidates first + r, first + r + world, ... -> all-gather of the
+                      k smallest accepted indices, merged; all-reduce(sum) of the stage counts
+  materialised streams  disjoint index ranges, each rank writes its own HBM; nothing is exchanged
+
+`engine` is a basebandboard_b200.lib.Context (the CUDA library).  The functions only use its
+public methods, so the CPU tests drive the same logic with a stand-in engine over the oracle.
+"""
+import numpy as np
+
+
+def split_range(first, count, rank, world):
+    """Contiguous near-equal split of [first, first+count): returns (first_r, count_r)."""
+    per, extra = divmod(count, world)
+    lo = first + rank * per + min(rank, extra)
+    return lo, per + (1 if rank < extra else 0)
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist if dist.is_available() and dist.is_initialized() else None
+
+
+def _device():
+    import torch
+    dist = _dist()
+    if dist is not None and dist.get_backend() == "nccl":
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
+def _all_reduce_sum_u64(values):
+    """Sum of uint64 vectors over ranks (two's complement wrap-around, carried as int64)."""
+    import torch
+    dist = _dist()
+    a = np.ascontiguousarray(values, dtype=np.uint64)
+    if dist is None or dist.get_world_size() == 1:
+        return a.copy()
+    t = torch.from_numpy(a.view(np.int64).copy()).to(_device())
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t.cpu().numpy().view(np.uint64)
+
+
+def _all_gather_i64(values):
+    """[world, len(values)] int64 on every rank."""
+    import torch
+    dist = _dist()
+    a = np.ascontiguousarray(values, dtype=np.int64)
+    if dist is None or dist.get_world_size() == 1:
+        return a[None, :].copy()
+    t = torch.from_numpy(a.copy()).to(_device())
+    out = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return np.stack([o.cpu().numpy() for o in out])
+
+
+def rank_world():
+    dist = _dist()
+    return (dist.get_rank(), dist.get_world_size()) if dist is not None else (0, 1)
+
+
+# ------------------------------------------------------------------------------------------------
+def clt_hist_sharded(engine, init, first, count, model=0):
+    """Histogram and moments of g[first, first+count) computed by all ranks together."""
+    rank, world = rank_world()
+    lo, cnt = split_range(first, count, rank, world)
+    hist, s, ss = engine.clt_hist(init, lo, cnt, model)
+    acc = np.concatenate([hist.astype(np.uint64), np.array([s], dtype=np.int64).view(np.uint64),
+                          np.array([ss], dtype=np.uint64)])
+    acc = _all_reduce_sum_u64(acc)
+    return acc[:-2].copy(), int(acc[-2:-1].view(np.int64)[0]), int(acc[-1])
+
+
+def _det_tuple(det):
+    return (int(det.bit_in), int(det.prbs), int(det.err_sr), int(det.reload_ctr))
+
+
+def prbs_detect_sharded(engine, k, nbits, m=0, seed=1, first_bit=0, make_det=None):
+    """Counters of the detector over bits [first_bit, first_bit+nbits) cut contiguously over the
+    ranks.  `make_det(bit_in, prbs, err_sr, reload_ctr)` builds the engine's detector-state object
+    (default: basebandboard_b200.lib.DetState).  Returns (counters, final detector state tuple,
+    how many times this rank ran its range)."""
+    rank, world = rank_world()
+    if make_det is None:
+        from .lib import DetState as make_det
+    # cut on 64-bit word boundaries relative to first_bit so that every shard but the last is whole words
+    words = (nbits + 63) // 64
+    wlo, wcnt = split_range(0, words, rank, world)
+    lo = first_bit + 64 * wlo
+    cnt = max(0, min(64 * wcnt, first_bit + nbits - lo))
+    if rank == 0:
+        start = (0, 1, (1 << k) - 1, 0)               # reset values, prbs.py:62,80,90
+    else:
+        start = _det_tuple(engine.prbs_spec_state(k, lo, m, seed)) if lo >= 64 else (0, 1, (1 << k) - 1, 0)
+    runs = 0
+    while True:
+        det = make_det(*start)
+        ctr = engine.prbs_detect(k, cnt, m=m, seed=seed, first_bit=lo, det=det) if cnt else \
+            {"err": 0, "err_valid": 0, "reload_events": 0, "reload_cycles": 0, "injected": 0}
+        runs += 1
+        end = _det_tuple(det) if cnt else start
+        table = _all_gather_i64(list(start) + list(end))     # [world, 8]
+        # the state each rank should have started from: its left neighbour's end state
+        wrong = [r for r in range(1, world) if tuple(table[r][:4]) != tuple(table[r - 1][4:])]
+        if not wrong:
+            break
+        if rank in wrong:
+            start = tuple(int(v) for v in table[rank - 1][4:])
+    keys = ("err", "err_valid", "reload_events", "reload_cycles", "injected")
+    tot = _all_reduce_sum_u64(np.array([ctr[key] for key in keys], dtype=np.uint64))
+    final = tuple(int(v) for v in table[world - 1][4:])
+    return dict(zip(keys, (int(v) for v in tot))), final, runs
+
+
+def rnghunt_sweep_sharded(engine, n, seed, first, count, k=16):
+    """Sweep candidates first .. first+count-1, rank r taking every world-th one; returns the k
+    smallest accepted candidate indices overall and the summed stage counts."""
+    rank, world = rank_world()
+    mine = len(range(rank, count, world))
+    res = engine.rnghunt_sweep(n, seed, first + rank, mine, k=k, stride=world) if mine else \
+        {"best": [], "stage_counts": np.zeros(5, dtype=np.uint64)}
+    best = list(res["best"])[:k]
+    pad = np.full(k + 1, -1, dtype=np.int64)
+    pad[0] = len(best)
+    pad[1:1 + len(best)] = best
+    allb = _all_gather_i64(pad)
+    merged = sorted(int(v) for row in allb for v in row[1:1 + int(row[0])])[:k]
+    counts = _all_reduce_sum_u64(np.asarray(res["stage_counts"], dtype=np.uint64))
+    return {"best": merged, "stage_counts": counts}
+
+
+def stream_shard(first, count, align=64):
+    """This rank's disjoint slice of a materialised stream, aligned to `align` units."""
+    rank, world = rank_world()
+    units = (count + align - 1) // align
+    ulo, ucnt = split_range(0, units, rank, world)
+    lo = first + ulo * align
+    return lo, max(0, min(ucnt * align, first + count - lo))

@@ -168,7 +168,7 @@ int bbb_prbs_detect(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits
 /* The state a locked detector with no reload pending has just before bit first_bit (>= 64) of that
  * channel: what a shard that does not start at bit 0 passes as `det` before it has its left
  * neighbour's end state; the caller compares the two and re-runs the shard on a mismatch
- * (basebandboard_b200/sharding.py).  Pure host arithmetic. */
+ * (basebandboard_b200/sharding.py).  Pure host arithmetic: ctx may be NULL and no GPU is needed. */
 int bbb_prbs_spec_state(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint32_t err_m, uint64_t seed,
                         bbb_det_state *det);
 

@@ -40,6 +40,24 @@ def main():
                 print(json.dumps({"what": "prbs_detect", "k": k, "m": m, "bits": nbits, "ms": ms,
                                   "rounds": c.last_rounds, "launches": c.last_launches,
                                   "Tbit_s": nbits / ms / 1e9, "counters": r}), flush=True)
+    if "streams" in what:
+        c.lutopt_load_shipped(256)
+        for name, count, bytes_per in (("clt_stream_i8", 1 << 31, 1), ("clt_stream_i16", 1 << 30, 2),
+                                       ("lutopt_stream", 1 << 26, 32)):
+            buf = torch.empty(count * bytes_per, dtype=torch.uint8, device="cuda")
+            ms = []
+            for _ in range(3):
+                if name == "lutopt_stream":
+                    c.lutopt_stream_dev(1, 0, count, buf.data_ptr())
+                else:
+                    c.clt_stream_dev(1, 0, count, 0, 8 if bytes_per == 2 else 1, buf.data_ptr(), bytes_per)
+                c.sync()
+                ms.append(c.last_device_ms)
+            print(json.dumps({"what": name, "count": count, "bytes": count * bytes_per, "ms": ms,
+                              "kernel": c.last_kernel, "launches": c.last_launches,
+                              "GBps_best": count * bytes_per / min(ms) / 1e6,
+                              "Gsamples_s": count / min(ms) / 1e6}), flush=True)
+            del buf
     if "rnghunt" in what:
         for n in (64, 128, 192, 256):
             cnt = 1 << 18
