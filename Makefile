@@ -9,7 +9,7 @@ SRCS      := $(wildcard $(CSRC)/*.cu)
 OBJS      := $(patsubst $(CSRC)/%.cu,build/%.o,$(SRCS))
 HDRS      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh $(CSRC)/*.inc) include/bbb_b200.h
 
-all: $(LIB) oracle
+all: $(LIB) oracle cli/rnghunt
 
 build/%.o: $(CSRC)/%.cu $(HDRS)
 	@mkdir -p build
@@ -21,8 +21,12 @@ $(LIB): $(OBJS)
 oracle:
 	$(MAKE) -C oracle
 
+# drop-in for the reference's rnghunt binary (software/rnghunt/src/bin/rnghunt.rs), C++ over the C ABI
+cli/rnghunt: cli/rnghunt.cpp include/bbb_b200.h $(LIB)
+	g++ -O2 -std=c++17 -Wall -o $@ cli/rnghunt.cpp -Lbasebandboard_b200 -lbbb_b200 -Wl,-rpath,'$$ORIGIN/../basebandboard_b200'
+
 clean:
-	rm -rf build $(LIB)
+	rm -rf build $(LIB) cli/rnghunt
 	$(MAKE) -C oracle clean
 
 .PHONY: all oracle clean
