@@ -154,6 +154,123 @@ def workload_config(args, world):
     }
 
 
+def run_secondary(args, ctx, rank, world, local_rank):
+    """The other BASELINE.json configs through the same contract (device-timed value, e2e through the
+    host-buffer API, max over ranks, clocks).  One JSON line from rank 0."""
+    import torch
+    import torch.distributed as dist
+    from basebandboard_b200 import lib, sharding
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    hbm_peak = None
+    try:
+        hbm_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:
+        pass
+    w = args.workload
+    extra = {}
+    if w == "prbs_stream":
+        nbits = 1 << args.log2_bits
+        first = rank * nbits
+        buf = torch.empty(nbits // 64, dtype=torch.int64, device="cuda")
+        def step():
+            ctx.prbs_stream_dev(args.k, nbits, buf.data_ptr(), first_bit=first)
+            return ctx.last_launches
+        def step_e2e():          # host buffer out: the D2H copy of the packed stream is inside the timed region
+            n = min(nbits, 1 << 33)
+            ctx.prbs_stream(args.k, n, first_bit=first)
+            return n, ctx.last_h2d_bytes, ctx.last_d2h_bytes
+        units, metric, unit, scale = nbits, "prbs_stream_gbytes_per_s", "GB/s", 1 / 8e9
+        workload = "PRBS-%d packed stream materialised to HBM, 2^%d bits/GPU (BASELINE.json configs[4])" % (args.k, args.log2_bits)
+        dtype = "u64 (GF(2) word recurrence)"
+        l2 = "output (%d MiB) exceeds L2; nothing is read" % (nbits >> 23)
+    elif w == "prbs_detect":
+        nbits = 1 << args.log2_bits
+        first = rank * nbits
+        def step():
+            det = lib.DetState(*((0, 1, (1 << args.k) - 1, 0) if rank == 0 else
+                                 sharding._det_tuple(lib.prbs_spec_state(args.k, first, args.err_m, 1))))
+            extra["ctr"] = ctx.prbs_detect(args.k, nbits, m=args.err_m, seed=1, first_bit=first, det=det)
+            extra["rounds"] = ctx.last_rounds
+            return ctx.last_launches
+        def step_e2e():
+            step()
+            return nbits, ctx.last_h2d_bytes + 16, ctx.last_d2h_bytes
+        units, metric, unit, scale = nbits, "prbs_detect_tbit_per_s", "Tbit/s", 1e-12
+        workload = ("PRBS-%d generate + Bernoulli(2^-%d) channel + self-synchronising error count, 2^%d bits/GPU "
+                    "(BASELINE.json configs[1])" % (args.k, args.err_m, args.log2_bits))
+        dtype = "u32/u64 integer"
+        l2 = "no HBM-resident input"
+    else:
+        cnt = 1 << args.log2_candidates
+        def step():
+            extra["res"] = ctx.rnghunt_sweep(args.hunt_n, 1, rank, cnt, k=16, stride=world)
+            return ctx.last_launches
+        def step_e2e():
+            step()
+            return cnt, ctx.last_h2d_bytes, ctx.last_d2h_bytes
+        units, metric, unit, scale = cnt, "rnghunt_candidates_per_s", "candidates/s", 1.0
+        workload = ("rnghunt sweep n=%d, seed 1, 2^%d candidates/GPU interleaved over ranks, best-16 "
+                    "(BASELINE.json configs[3])" % (args.hunt_n, args.log2_candidates))
+        dtype = "u32 GF(2)"
+        l2 = "no HBM-resident input"
+
+    for _ in range(args.warmup):
+        step()
+        ctx.sync()
+    barrier()
+    sampler = ClockSampler(physical_gpu_index(local_rank))
+    sampler.start()
+    launches = 0
+    dev_ms = 0.0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        launches += step()
+        ctx.sync()
+        dev_ms += ctx.last_device_ms
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.finish()
+    barrier()
+    t1 = time.perf_counter()
+    e_units, h2d, d2h = step_e2e()
+    e2e_ms = (time.perf_counter() - t1) * 1e3
+    t = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms, e2e_ms = [float(v) for v in t.cpu()]
+    if rank == 0:
+        value = world * units * args.steps / (dev_ms * 1e-3) * scale
+        line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": dtype, "data": "synthetic",
+                "config": {"workload": workload, "l2": l2},
+                "wall_ms_per_step": wall_ms / args.steps, "clocks": clocks,
+                "e2e": {"value": world * e_units / (e2e_ms * 1e-3) * scale, "unit": unit,
+                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                "gpu_launches": launches}
+        if w == "prbs_stream" and hbm_peak:
+            ach = units / 8 / (dev_ms / args.steps * 1e-3) / 1e9
+            line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                                "frac": ach / hbm_peak, "traffic": None,
+                                "note": "algorithmic bytes = 1/8 B per PRBS bit; peak = measured copy bandwidth "
+                                        "(MEASURED_PEAKS.json), per GPU"}
+        if "ctr" in extra:
+            line["result_check"] = dict(extra["ctr"], rounds=extra["rounds"])
+        if "res" in extra:
+            line["result_check"] = {"best": extra["res"]["best"],
+                                    "stage_counts": [int(v) for v in extra["res"]["stage_counts"]]}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -161,6 +278,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--log2-samples", type=int, default=40)
+    ap.add_argument("--workload", default="clt_fused",
+                    choices=["clt_fused", "prbs_stream", "prbs_detect", "rnghunt"],
+                    help="clt_fused = the headline (BASELINE.json configs[2]); the others are the remaining "
+                         "BASELINE configs, same JSON contract, their own metric")
+    ap.add_argument("--k", type=int, default=31, help="PRBS order for the prbs_* workloads")
+    ap.add_argument("--log2-bits", type=int, default=36, help="PRBS bits per GPU per step")
+    ap.add_argument("--err-m", type=int, default=10, help="prbs_detect channel error probability 2^-m")
+    ap.add_argument("--hunt-n", type=int, default=192)
+    ap.add_argument("--log2-candidates", type=int, default=20, help="rnghunt candidates per GPU per step")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample length")
     ap.add_argument("--ref-step-seconds", type=float, default=4.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -184,6 +310,8 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = lib.Context(local_rank)
+    if args.workload != "clt_fused":
+        return run_secondary(args, ctx, rank, world, local_rank)
     ctx.lutopt_load_shipped(N_STATE)
     count = 1 << args.log2_samples
     first = rank * count
