@@ -268,10 +268,10 @@ def rmw_hooks(words, first_slot=0):
     return hooks
 
 
-def gen_transpose(em, q):
-    """8x8 bit-block transpose of planes q[0..5] (q6 = q7 = 0): on return byte m of word s holds
-    the 6-bit value of stream 8m+s.  Writes z0..z7."""
-    x = list(q) + ["0u", "0u"]
+def gen_transpose(em, q, out="z%d", decl=""):
+    """8x8 bit-block transpose of up to 8 planes q[0..] (missing ones are 0): on return byte m of
+    word s holds the value (bit b = plane b) of stream 8m+s.  Writes out % s for s = 0..7."""
+    x = list(q) + ["0u"] * (8 - len(q))
     for sh, mask in ((4, "0x0f0f0f0fu"), (2, "0x33333333u"), (1, "0x55555555u")):
         y = [None] * 8
         for i in range(8):
@@ -284,22 +284,55 @@ def gen_transpose(em, q):
             y[i], y[i + sh] = nl, nh
         x = y
     for s in range(8):
-        em.emit("z%d = %s;" % (s, x[s]))
+        em.emit("%s%s = %s;" % (decl, out % s, x[s]))
 
 
-def main():
-    rows = recurrences.packed(N)
-    iters = int(os.environ.get("CLT256_ANNEAL_ITERS", "1500000"))
-    pos, cost = optimise_perm(rows, iters, W=WINDOW, verbose=True)
-    perm = [0] * N
-    for b, p in enumerate(pos):
-        perm[p] = b
+def optimise_perm_words(rows, iters, seed=777, W=WINDOW):
+    """Like optimise_perm, with the constraint the raw-word stream kernel needs: state bits 0..127
+    (output words 0..3) are stored at positions 0..127, bits 128..255 at 128..255, so that all 32
+    planes of an output word are accumulators of the same pass.  Swaps stay inside a half."""
+    rnd = random.Random(seed)
+    pos = list(range(N))
+    uses = [[] for _ in range(N)]
+    for r in range(N):
+        for t in rows[r]:
+            uses[t].append(r)
+    rc = [row_cost(sorted(pos[t] for t in rows[r]), W) for r in range(N)]
+    cur = sum(rc)
+    best, best_pos = cur, pos[:]
+    T0, T1 = 1.5, 0.05
+    for it in range(iters):
+        T = T0 * (T1 / T0) ** (it / iters)
+        a = rnd.randrange(N)
+        b = rnd.randrange(HALF) + (HALF if a >= HALF else 0)
+        if a == b:
+            continue
+        aff = set(uses[a]) | set(uses[b])
+        pos[a], pos[b] = pos[b], pos[a]
+        new = {r: row_cost(sorted(pos[t] for t in rows[r]), W) for r in aff}
+        d = sum(new.values()) - sum(rc[r] for r in aff)
+        if d <= 0 or rnd.random() < pow(2.718281828, -d / T):
+            for r, v in new.items():
+                rc[r] = v
+            cur += d
+            if cur < best:
+                best, best_pos = cur, pos[:]
+        else:
+            pos[a], pos[b] = pos[b], pos[a]
+    return best_pos, best
+
+
+def emit_store(em, dst):
+    for g in range(32):
+        em.emit("%s[%d * CLT256_B] = make_uint4(a%d, a%d, a%d, a%d);" % (dst, g, 4 * g, 4 * g + 1, 4 * g + 2, 4 * g + 3))
+
+
+def body_hist(rows, pos, perm):
     em = Emitter()
     em.emit("uint32_t " + ", ".join("a%d" % i for i in range(HALF)) + ";")
     em.emit("// ---- pass 1: new planes of storage positions 0..127 + popcount network ----")
     planes = gen_pass(em, rows, pos, perm, 0, True, rmw_hooks([4, 5, 6, 7]))
-    for g in range(32):
-        em.emit("lo_new[%d * CLT256_B] = make_uint4(a%d, a%d, a%d, a%d);" % (g, 4 * g, 4 * g + 1, 4 * g + 2, 4 * g + 3))
+    emit_store(em, "lo_new")
     em.emit("// ---- popcount planes -> histogram index planes ----")
     for w in range(9):
         em.emit("const uint32_t pc%d = %s;" % (w, planes[w]))
@@ -313,21 +346,77 @@ def main():
     gen_transpose(em, q)
     em.emit("// ---- pass 2: new planes of storage positions 128..255 ----")
     gen_pass(em, rows, pos, perm, 1, False, rmw_hooks([0, 1, 2, 3]))
-    for g in range(32):
-        em.emit("hi[%d * CLT256_B] = make_uint4(a%d, a%d, a%d, a%d);" % (g, 4 * g, 4 * g + 1, 4 * g + 2, 4 * g + 3))
+    emit_store(em, "hi")
+    return em
 
-    out = os.path.join(ROOT, "basebandboard_b200", "csrc", "clt256_gen.inc")
+
+def body_s8(rows, pos, perm):
+    """int8 sample stream: the low 8 popcount planes with bit 7 flipped are g = popcount - 128 in
+    two's complement (gateware width, rng.py:78); un-sliced to one byte per stream."""
+    em = Emitter()
+    em.emit("uint32_t " + ", ".join("a%d" % i for i in range(HALF)) + ";")
+    planes = gen_pass(em, rows, pos, perm, 0, True, {})
+    emit_store(em, "lo_new")
+    for w in range(9):
+        em.emit("const uint32_t pc%d = %s;" % (w, planes[w]))
+    em.emit("const uint32_t pc7n = ~pc7;")
+    gen_transpose(em, ["pc0", "pc1", "pc2", "pc3", "pc4", "pc5", "pc6", "pc7n"], out="zs%d", decl="const uint32_t ")
+    em.emit("CLT256_S8_STAGE(zs0, zs1, zs2, zs3, zs4, zs5, zs6, zs7, pc8)")
+    gen_pass(em, rows, pos, perm, 1, False, {})
+    emit_store(em, "hi")
+    return em
+
+
+def body_words(rows, pos, perm):
+    """raw URNG words: after each pass the 128 new planes (state bits 0..127, then 128..255) are stored
+    to shared memory and handed, in state-bit order, to CLT256_W_EMIT for the 32x32 transposes."""
+    em = Emitter()
+    em.emit("uint32_t " + ", ".join("a%d" % i for i in range(HALF)) + ";")
+    for which, dst in ((0, "lo_new"), (1, "hi")):
+        gen_pass(em, rows, pos, perm, which, False, {})
+        emit_store(em, dst)
+        for w in range(4):
+            bits = range(128 * which + 32 * w, 128 * which + 32 * w + 32)
+            regs = ", ".join("a%d" % (pos[b] - 128 * which) for b in bits)
+            em.emit("CLT256_W_EMIT(%d, %s)" % (4 * which + w, regs))
+        em.emit("CLT256_W_STORE(%d)" % which)
+    return em
+
+
+def write_inc(name, title, perm, em, cost, prefix):
+    out = os.path.join(ROOT, "basebandboard_b200", "csrc", name)
     with open(out, "w") as f:
-        f.write("// GENERATED by tools/gen_clt256.py -- do not edit.  One LUTOPT(n256) clock + CLTGRNG popcount\n")
-        f.write("// network on 32 bit-sliced streams (rng.py:38-40, :96-105; rng_recurrences.py:172-259).\n")
+        f.write("// GENERATED by tools/gen_clt256.py -- do not edit.  %s\n" % title)
+        f.write("// on 32 bit-sliced streams (rng.py:38-40, :96-105; rng_recurrences.py:172-259).\n")
         f.write("// recurrence instructions: %d (cost model %d), carry-save adders: %d, half adders: %d, window %d\n"
                 % (em.ops["rec"], cost, em.ops["csa"], em.ops["ha"], WINDOW))
-        f.write("#ifdef CLT256_SECTION_PERM\n// storage position p holds state bit CLT256_PERM[p]\n")
-        f.write("static __constant__ uint8_t CLT256_PERM[256] = {%s};\n" % ", ".join(str(v) for v in perm))
-        f.write("#endif\n#ifdef CLT256_SECTION_BODY\n")
+        if perm is not None:
+            f.write("#ifdef %s_SECTION_PERM\n// storage position p holds state bit %s_PERM[p]\n" % (prefix, prefix))
+            f.write("static __constant__ uint8_t %s_PERM[256] = {%s};\n" % (prefix, ", ".join(str(v) for v in perm)))
+            f.write("#endif\n")
+        f.write("#ifdef %s_SECTION_BODY\n" % prefix)
         f.write("\n".join(em.lines))
         f.write("\n#endif\n")
     print("wrote", out, "ops", em.ops, "cost model", cost, file=sys.stderr)
+
+
+def main():
+    rows = recurrences.packed(N)
+    iters = int(os.environ.get("CLT256_ANNEAL_ITERS", "1500000"))
+    pos, cost = optimise_perm(rows, iters, W=WINDOW, verbose=True)
+    perm = [0] * N
+    for b, p in enumerate(pos):
+        perm[p] = b
+    write_inc("clt256_gen.inc", "One LUTOPT(n256) clock + CLTGRNG popcount network + histogram indices",
+              perm, body_hist(rows, pos, perm), cost, "CLT256")
+    write_inc("clt256_s8_gen.inc", "One LUTOPT(n256) clock + CLTGRNG popcount network -> int8 samples (same storage order as clt256_gen.inc)",
+              None, body_s8(rows, pos, perm), cost, "CLT256S8")
+    wpos, wcost = optimise_perm_words(rows, iters, W=WINDOW)
+    wperm = [0] * N
+    for b, p in enumerate(wpos):
+        wperm[p] = b
+    write_inc("clt256_words_gen.inc", "One LUTOPT(n256) clock -> raw URNG words",
+              wperm, body_words(rows, wpos, wperm), wcost, "CLT256W")
 
 
 if __name__ == "__main__":
