@@ -167,6 +167,7 @@ void bbb_destroy(bbb_ctx *c)
     if (c->d_row_ptr) cudaFree(c->d_row_ptr);
     if (c->d_taps) cudaFree(c->d_taps);
     bbb_prbs_free_tables(c);
+    for (auto &js : c->jump_sets) if (js.dev) cudaFree(js.dev);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaEventDestroy(c->evt0);
@@ -256,8 +257,7 @@ int bbb_lutopt_load(bbb_ctx *c, uint32_t n, const uint32_t *row_ptr, const uint1
         for (uint32_t j = row_ptr[r]; j < row_ptr[r + 1]; j++)
             c->A.row(r)[taps[j] >> 6] ^= 1ull << (taps[j] & 63);   // XOR: a repeated tap cancels
     c->Apow2.clear();
-    c->jump_key_L = 0;
-    c->jump_key_bits = 0;
+    for (auto &js : c->jump_sets) { js.L = 0; js.nbits = 0; }
     if (c->d_row_ptr) cudaFree(c->d_row_ptr);
     if (c->d_taps) cudaFree(c->d_taps);
     c->d_row_ptr = nullptr;

@@ -60,8 +60,14 @@ struct bbb_ctx {
     void *prbs_host[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     void *prbs_dev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     // cached jump-ahead operators on the device (scratch slot 0)
-    uint64_t jump_key_L = 0;
-    uint32_t jump_key_bits = 0;
+    struct JumpSet {              // A^(L*2^b), b < nbits, column-major u32, on the device
+        uint64_t L = 0;
+        uint32_t nbits = 0;
+        uint32_t *dev = nullptr;
+        size_t bytes = 0;
+        uint64_t stamp = 0;
+    } jump_sets[4];
+    uint64_t jump_stamp = 0;
     HostMat A;                    // dense A
     std::vector<HostMat> Apow2;   // A^(2^i), grown on demand
     uint32_t *d_row_ptr = nullptr;   // device copies for the generic kernel

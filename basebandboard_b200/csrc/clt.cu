@@ -238,6 +238,9 @@ static int launch_seed(bbb_ctx *c, const uint32_t *dJ, const SeedStart &xs, uint
 int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only);
 int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model, const uint32_t *planes,
                         unsigned long long *hist);
+int bbb_clt_spec_stream_ok(const bbb_ctx *c, int kind);
+int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L, const uint32_t *planes, void *out,
+                               uint32_t noise_var);
 
 // Uploads the jump-ahead operators A^(L*2^b), b < nbits, column-major 32-bit words, into scratch
 // slot 0 (kept across calls while (L, nbits) repeat).  Returns the device pointer or null.
@@ -245,10 +248,25 @@ static uint32_t *upload_jump_ops(bbb_ctx *c, uint64_t L, uint32_t nbits)
 {
     const uint32_t n = c->n, nw32 = (n + 31) / 32;
     const size_t per = (size_t)n * nw32;
-    uint32_t *dJ = (uint32_t *)c->scratch(0, (nbits ? nbits : 1) * per * 4);
-    if (!dJ) return nullptr;
-    if (c->jump_key_L == L && c->jump_key_bits >= nbits && nbits) return dJ;
-    c->jump_key_L = 0;
+    // a few (L, nbits) geometries recur from call to call (a straight-line launch and its tail):
+    // keep the four most recently used operator sets on the device
+    bbb_ctx::JumpSet *slot = &c->jump_sets[0];
+    for (auto &js : c->jump_sets) {
+        if (js.L == L && js.nbits >= nbits && nbits && js.dev) { js.stamp = ++c->jump_stamp; return js.dev; }
+        if (js.stamp < slot->stamp) slot = &js;
+    }
+    const size_t bytes = (nbits ? nbits : 1) * per * 4;
+    if (slot->bytes < bytes) {
+        if (slot->dev) cudaFree(slot->dev);
+        slot->dev = nullptr;
+        slot->bytes = 0;
+        if (cudaMalloc(&slot->dev, bytes) != cudaSuccess) { c->cuda_fail(cudaGetLastError(), "cudaMalloc(jump operators)"); return nullptr; }
+        slot->bytes = bytes;
+    }
+    slot->L = 0;
+    slot->nbits = 0;
+    slot->stamp = ++c->jump_stamp;
+    uint32_t *dJ = slot->dev;
     if (!nbits) return dJ;
     std::vector<uint32_t> all(nbits * per), one;
     HostMat M;
@@ -272,8 +290,8 @@ static uint32_t *upload_jump_ops(bbb_ctx *c, uint64_t L, uint32_t nbits)
         c->cuda_fail(cudaGetLastError(), "upload jump operators");
         return nullptr;
     }
-    c->jump_key_L = L;
-    c->jump_key_bits = nbits;
+    slot->L = L;
+    slot->nbits = nbits;
     return dJ;
 }
 
@@ -312,22 +330,34 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
     const uint64_t Sres = (uint64_t)c->sm_count * Bg * 32;
     const uint32_t Lmin = 64;
 
-    const bool hist_only = d_hist && !d_out8 && !d_out16 && !d_out_words32;
-    const uint64_t spb = (uint64_t)bbb_clt_spec_streams_per_block(c, hist_only);
+    // which straight-line kernel of the shipped n256 matrix applies: 0 fused histogram, 1 int8 samples,
+    // 2 raw words, 3 int16 scaled samples, -1 none
+    int kind = -1;
+    if (d_hist && !d_out8 && !d_out16 && !d_out_words32) kind = 0;
+    else if (d_out8 && !d_hist && !d_out16 && !d_out_words32 && ((uintptr_t)d_out8 & 7) == 0) kind = 1;
+    else if (d_out_words32 && !d_hist && !d_out8 && !d_out16 && ((uintptr_t)d_out_words32 & 15) == 0) kind = 2;
+    else if (d_out16 && !d_hist && !d_out8 && !d_out_words32 && ((uintptr_t)d_out16 & 15) == 0) kind = 3;
+    uint64_t spb = 0;
+    if (kind == 0) spb = (uint64_t)bbb_clt_spec_streams_per_block(c, true);
+    else if (kind > 0 && bbb_clt_spec_stream_ok(c, kind)) spb = (uint64_t)bbb_clt_spec_streams_per_block(c, true);
 
     uint64_t done = 0;
     c->last_kernel = "generic";
     while (done < count) {
         const uint64_t rem = count - done;
 
-        // ---- specialised fused kernel: `blocks` CTAs x spb streams x L clocks, one wave ----
-        if (spb) {
+        // ---- specialised kernel: `blocks` CTAs x spb streams x L clocks, one wave ----
+        if (spb && ((kind != 1 && kind != 3) || (done & 7) == 0)) {
             const uint64_t max_blocks = c->tune_spec_max_blocks ? c->tune_spec_max_blocks : (uint64_t)c->sm_count;
-            uint64_t blocks = rem / (spb * c->tune_spec_min_steps);
+            // fewest clocks per stream worth a launch (the stream kernels amortise their seeding sooner)
+            const uint64_t min_steps = kind > 0 ? (c->tune_spec_min_steps / 4 > 8 ? c->tune_spec_min_steps / 4 : 8)
+                                                : c->tune_spec_min_steps;
+            uint64_t blocks = rem / (spb * min_steps);
             if (blocks > max_blocks) blocks = max_blocks;
-            if (blocks >= 1) {
-                uint64_t L = rem / (blocks * spb);
-                if (L > (1ull << 26)) L = 1ull << 26;      // private u32 bins: 32 * L < 2^32
+            uint64_t L = blocks ? rem / (blocks * spb) : 0;
+            if (L > (1ull << 26)) L = 1ull << 26;          // private u32 bins: 32 * L < 2^32
+            if (kind == 1 || kind == 3) L &= ~7ull;         // 8 clocks per store
+            if (blocks >= 1 && L >= 8) {
                 const uint64_t S = blocks * spb;
                 const uint32_t T = (uint32_t)(S / 32);
                 uint32_t nbits = 0;
@@ -336,16 +366,24 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
                 if (!dJ) return BBB_ECUDA;
                 uint32_t *d_planes = (uint32_t *)c->scratch(1, (size_t)n * T * 4);
                 if (!d_planes) return BBB_ECUDA;
-                // the kernel takes the CLT of a stream's state BEFORE each clock: start one clock in
+                // the CLT kernels take the tree of a stream's state BEFORE each clock: start one clock in;
+                // the raw-word kernel emits the state AFTER each clock
                 uint64_t x1[BBB_MAX_NW64];
                 memcpy(x1, xl, sizeof x1);
-                advance_state(c, x1, 1);
+                if (kind != 2) advance_state(c, x1, 1);
                 SeedStart xs;
                 to_seed(x1, nw64, xs);
                 int rc = launch_seed(c, dJ, xs, nbits, T, d_planes);
                 if (rc) return rc;
-                rc = bbb_clt_spec_launch(c, (uint32_t)blocks, (uint32_t)L, model, d_planes,
-                                         (unsigned long long *)d_hist);
+                if (kind == 0)
+                    rc = bbb_clt_spec_launch(c, (uint32_t)blocks, (uint32_t)L, model, d_planes,
+                                             (unsigned long long *)d_hist);
+                else
+                    rc = bbb_clt_spec_stream_launch(c, kind, (uint32_t)blocks, (uint32_t)L, d_planes,
+                                                    kind == 1 ? (void *)(d_out8 + done)
+                                                    : kind == 3 ? (void *)(d_out16 + done)
+                                                                : (void *)(d_out_words32 + done * 8),
+                                                    noise_var);
                 if (rc) return rc;
                 advance_state(c, xl, S * L);
                 done += S * L;

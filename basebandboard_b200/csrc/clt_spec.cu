@@ -123,3 +123,193 @@ int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model,
     c->last_kernel = "clt256_fused";
     return BBB_OK;
 }
+
+// ===========================================================================
+// materialised streams of the shipped n256 recurrence
+// ===========================================================================
+#define CLT256S8_STAGE_BYTES (16 * CLT256_B * 16)
+#define CLT256S8_SMEM (CLT256_STATE_BYTES + CLT256S8_STAGE_BYTES)
+
+// int8 samples g[i] (gateware width): 8 clocks are staged in shared memory as un-sliced bytes
+// (word s of clock tau: byte m = sample of stream 8m+s), then each stream's 8 bytes leave as one
+// 64-bit store; sectors are completed in L2 by the following flushes.
+#define CLT256_S8_STAGE(z0, z1, z2, z3, z4, z5, z6, z7, pc8)                  \
+    stage[((it & 7u) * 2u) * CLT256_B] = make_uint4(z0, z1, z2, z3);          \
+    stage[((it & 7u) * 2u + 1u) * CLT256_B] = make_uint4(z4, z5, z6, z7);
+
+__device__ __forceinline__ void bytes4x4(uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t (&o)[4])
+{
+    const uint32_t ab_lo = __byte_perm(a, b, 0x5140), ab_hi = __byte_perm(a, b, 0x7362);
+    const uint32_t cd_lo = __byte_perm(c, d, 0x5140), cd_hi = __byte_perm(c, d, 0x7362);
+    o[0] = __byte_perm(ab_lo, cd_lo, 0x5410);
+    o[1] = __byte_perm(ab_lo, cd_lo, 0x7632);
+    o[2] = __byte_perm(ab_hi, cd_hi, 0x5410);
+    o[3] = __byte_perm(ab_hi, cd_hi, 0x7632);
+}
+
+// four int8 samples of one word -> four int16 samples times noise_var (tx.py:75-76)
+__device__ __forceinline__ int32_t sext_byte(uint32_t x, uint32_t sel)
+{
+    uint32_t d;   // prmt with the selector's bit 3 set replicates the sign of the chosen byte
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(x), "r"(0u), "r"(sel));
+    return (int32_t)d;
+}
+
+__device__ __forceinline__ uint2 scale4(uint32_t x, int32_t nv)
+{
+    const int32_t s0 = sext_byte(x, 0x8880u) * nv, s1 = sext_byte(x, 0x9991u) * nv;
+    const int32_t s2 = sext_byte(x, 0xAAA2u) * nv, s3 = sext_byte(x, 0xBBB3u) * nv;
+    return make_uint2(__byte_perm((uint32_t)s0, (uint32_t)s1, 0x5410), __byte_perm((uint32_t)s2, (uint32_t)s3, 0x5410));
+}
+
+// noise_var < 0: out is int8 g[i]; otherwise out is int16 g[i] * noise_var.  (A run-time flag, not a
+// template parameter: cudafe++ needs tens of minutes to instantiate a template around the generated body.)
+__global__ void __launch_bounds__(CLT256_B, 1)
+clt256_s8_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, int8_t *__restrict__ out, int32_t noise_var)
+{
+    const bool OUT16 = noise_var >= 0;
+    extern __shared__ uint4 smem4[];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * CLT256_B + tid;
+    char *smb = (char *)smem4;
+    {
+        uint32_t *sw = (uint32_t *)smem4;
+        for (uint32_t p = 0; p < 256; p++) {
+            const uint32_t v = planes[(size_t)CLT256_PERM[p] * T + t];
+            const uint32_t G = p < 128 ? (p >> 2) : 64 + ((p - 128) >> 2);
+            sw[(G * CLT256_B + tid) * 4 + (p & 3)] = v;
+        }
+    }
+    __syncthreads();
+    uint4 *lo_old = smem4 + tid;
+    uint4 *lo_new = smem4 + 32 * CLT256_B + tid;
+    uint4 *const hi = smem4 + 64 * CLT256_B + tid;
+    uint4 *const stage = (uint4 *)(smb + CLT256_STATE_BYTES) + tid;
+    // stream j of this thread starts at sample offset j*L from outp
+    int8_t *const outp = out + (size_t)t * 32u * L * (OUT16 ? 2u : 1u);
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < L; it++) {
+#define CLT256S8_SECTION_BODY
+#include "clt256_s8_gen.inc"
+#undef CLT256S8_SECTION_BODY
+        uint4 *tmp = lo_old;
+        lo_old = lo_new;
+        lo_new = tmp;
+        if ((it & 7u) == 7u) {
+            uint4 Z[8][2];
+#pragma unroll
+            for (int tau = 0; tau < 8; tau++) {
+                Z[tau][0] = stage[(tau * 2) * CLT256_B];
+                Z[tau][1] = stage[(tau * 2 + 1) * CLT256_B];
+            }
+            int8_t *const o8 = outp + (size_t)(it - 7u) * (OUT16 ? 2u : 1u);
+#pragma unroll
+            for (int s = 0; s < 8; s++) {
+                uint32_t w[8], lo[4], hi4[4];
+#pragma unroll
+                for (int tau = 0; tau < 8; tau++) {
+                    const uint4 q = Z[tau][s >> 2];
+                    w[tau] = (s & 3) == 0 ? q.x : (s & 3) == 1 ? q.y : (s & 3) == 2 ? q.z : q.w;
+                }
+                bytes4x4(w[0], w[1], w[2], w[3], lo);
+                bytes4x4(w[4], w[5], w[6], w[7], hi4);
+#pragma unroll
+                for (int m = 0; m < 4; m++) {
+                    if (OUT16) {
+                        const uint2 a = scale4(lo[m], noise_var), b = scale4(hi4[m], noise_var);
+                        *(uint4 *)(o8 + (size_t)(8 * m + s) * L * 2u) = make_uint4(a.x, a.y, b.x, b.y);
+                    } else {
+                        *(uint2 *)(o8 + (size_t)(8 * m + s) * L) = make_uint2(lo[m], hi4[m]);
+                    }
+                }
+            }
+        }
+    }
+}
+
+// raw URNG words (LUTOPT.x after every clock, rng.py:27): 32 x 32 bit transposes of the new planes,
+// four 32-bit words of a stream leave as one 128-bit store (a stream's clock = one 32-byte sector)
+#define CLT256W_SECTION_PERM
+#include "clt256_words_gen.inc"
+#undef CLT256W_SECTION_PERM
+
+#define CLT256_W_EMIT(w, r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18, r19, \
+                      r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31)                                  \
+    {                                                                                                              \
+        uint32_t tw[32] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18,     \
+                           r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31};                        \
+        transpose32_fast(tw);                                                                                      \
+        _Pragma("unroll") for (int j = 0; j < 32; j++) wb[(w) & 3][j] = tw[j];                                     \
+    }
+
+#define CLT256_W_STORE(which)                                                                          \
+    {                                                                                                  \
+        uint32_t *const o32 = outp + (size_t)it * 8u + (which) * 4u;                                   \
+        _Pragma("unroll") for (int j = 0; j < 32; j++)                                                 \
+            __stcs((uint4 *)(o32 + (size_t)j * L * 8u), make_uint4(wb[0][j], wb[1][j], wb[2][j], wb[3][j])); \
+    }
+
+__global__ void __launch_bounds__(CLT256_B, 1)
+clt256_words_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * CLT256_B + tid;
+    {
+        uint32_t *sw = (uint32_t *)smem4;
+        for (uint32_t p = 0; p < 256; p++) {
+            const uint32_t v = planes[(size_t)CLT256W_PERM[p] * T + t];
+            const uint32_t G = p < 128 ? (p >> 2) : 64 + ((p - 128) >> 2);
+            sw[(G * CLT256_B + tid) * 4 + (p & 3)] = v;
+        }
+    }
+    __syncthreads();
+    uint4 *lo_old = smem4 + tid;
+    uint4 *lo_new = smem4 + 32 * CLT256_B + tid;
+    uint4 *const hi = smem4 + 64 * CLT256_B + tid;
+    uint32_t *const outp = out + (size_t)t * 32u * L * 8u;   // stream j, clock it: outp + (j*L + it)*8
+    uint32_t wb[4][32];
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < L; it++) {
+#define CLT256W_SECTION_BODY
+#include "clt256_words_gen.inc"
+#undef CLT256W_SECTION_BODY
+        uint4 *tmp = lo_old;
+        lo_old = lo_new;
+        lo_new = tmp;
+    }
+}
+
+// kind: 1 = int8 samples, 2 = raw words, 3 = int16 scaled samples
+int bbb_clt_spec_stream_ok(const bbb_ctx *c, int kind)
+{
+    (void)kind;
+    return c->shipped == 256 && !c->tune_no_spec;
+}
+
+int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L, const uint32_t *planes, void *out,
+                               uint32_t noise_var)
+{
+    if (kind == 1) {
+        static_assert(CLT256S8_SMEM <= 227 * 1024, "shared memory budget");
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_s8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256S8_SMEM));
+        clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out, -1);
+        c->last_kernel = "clt256_s8";
+    } else if (kind == 3) {
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_s8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256S8_SMEM));
+        clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
+                                                                             (int32_t)noise_var);
+        c->last_kernel = "clt256_s16";
+    } else {
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_words_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         CLT256_STATE_BYTES));
+        clt256_words_kernel<<<blocks, CLT256_B, CLT256_STATE_BYTES, c->stream>>>(planes, blocks * CLT256_B, L,
+                                                                                 (uint32_t *)out);
+        c->last_kernel = "clt256_words";
+    }
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    return BBB_OK;
+}

@@ -181,3 +181,88 @@ def test_spec256_equals_generic_large(ctx):
         ctx.set_tuning("clt_no_spec", 0)
     assert np.array_equal(a[0], b[0]) and a[1:] == b[1:]
     assert int(a[0].sum()) == 1 << 31
+
+
+# ---- the specialised n256 stream kernels (clt256_s8, clt256_words) ---------------------------------
+@pytest.mark.parametrize("blocks,min_steps,count,first", [(1, 8, 4096 * 24 + 77, 0), (2, 16, 2 * 4096 * 40 + 13, (1 << 33) + 5)])
+def test_spec256_int8_stream_matches_oracle(ctx, orc, blocks, min_steps, count, first):
+    """Straight-line kernel with on-chip bit->byte transpose and 64-bit stores + generic tail == oracle."""
+    ctx.lutopt_load_shipped(256)
+    ctx.set_tuning("clt_spec_min_steps", min_steps)
+    ctx.set_tuning("clt_spec_max_blocks", blocks)
+    try:
+        got = ctx.clt_stream(1, first, count, model=0)
+        ref = orc.clt_run(recurrences.packed(256), 1, first, count, model=0, want=("out8",))
+        assert np.array_equal(got, ref["out8"])
+    finally:
+        ctx.set_tuning("clt_spec_min_steps", 512)
+        ctx.set_tuning("clt_spec_max_blocks", 0)
+
+
+@pytest.mark.parametrize("blocks,min_steps,count,first", [(1, 8, 4096 * 9 + 5, 0), (2, 8, 2 * 4096 * 11 + 3, (1 << 35) + 1)])
+def test_spec256_word_stream_matches_oracle(ctx, orc, blocks, min_steps, count, first):
+    ctx.lutopt_load_shipped(256)
+    ctx.set_tuning("clt_spec_min_steps", min_steps)
+    ctx.set_tuning("clt_spec_max_blocks", blocks)
+    try:
+        got = ctx.lutopt_stream(1, first, count)
+        ref = orc.clt_run(recurrences.packed(256), 1, first, count, model=1, want=("words",))["words"]
+        assert np.array_equal(got.reshape(-1), ref)
+    finally:
+        ctx.set_tuning("clt_spec_min_steps", 512)
+        ctx.set_tuning("clt_spec_max_blocks", 0)
+
+
+def test_spec256_streams_equal_generic_large(ctx):
+    """Full-geometry launches (148 CTAs): specialised stream kernels == data-driven kernel, and the
+    int8 stream's histogram == the fused kernel's histogram over the same range."""
+    import torch
+    ctx.lutopt_load_shipped(256)
+    count = 148 * 4096 * 512 + 4096 * 3 + 7
+    a = torch.empty(count, dtype=torch.int8, device="cuda")
+    b = torch.empty(count, dtype=torch.int8, device="cuda")
+    ctx.clt_stream_dev(1, 99, count, 0, 1, a.data_ptr(), 1)
+    ctx.sync()
+    assert ctx.last_kernel in ("clt256_s8", "generic") and ctx.last_launches >= 2
+    ctx.set_tuning("clt_no_spec", 1)
+    try:
+        ctx.clt_stream_dev(1, 99, count, 0, 1, b.data_ptr(), 1)
+        ctx.sync()
+    finally:
+        ctx.set_tuning("clt_no_spec", 0)
+    assert bool(torch.equal(a, b))
+    h, s, ss = ctx.clt_hist(1, 99, count, 0)
+    hist = torch.bincount(a.to(torch.int64) + 128, minlength=256).cpu().numpy().astype(np.uint64)
+    assert np.array_equal(hist, h) and int(a.to(torch.int64).sum()) == s
+    del a, b
+    wc = 148 * 4096 * 512 // 8 + 333
+    wa = torch.empty(wc * 4, dtype=torch.int64, device="cuda")
+    wb = torch.empty(wc * 4, dtype=torch.int64, device="cuda")
+    ctx.set_tuning("clt_spec_min_steps", 64)
+    try:
+        ctx.lutopt_stream_dev(1, 5, wc, wa.data_ptr())
+        ctx.sync()
+        ctx.set_tuning("clt_no_spec", 1)
+        ctx.lutopt_stream_dev(1, 5, wc, wb.data_ptr())
+        ctx.sync()
+    finally:
+        ctx.set_tuning("clt_no_spec", 0)
+        ctx.set_tuning("clt_spec_min_steps", 512)
+    assert bool(torch.equal(wa, wb))
+
+
+@pytest.mark.parametrize("noise_var", [0, 1, 8, 15])
+def test_spec256_int16_noise_stream_matches_oracle(ctx, orc, noise_var):
+    """tx.py:75-76: noise = g * noise_var as int16, straight-line kernel + generic tail == oracle."""
+    ctx.lutopt_load_shipped(256)
+    ctx.set_tuning("clt_spec_min_steps", 16)
+    ctx.set_tuning("clt_spec_max_blocks", 2)
+    try:
+        count, first = 2 * 4096 * 24 + 21, 1234567
+        got = ctx.clt_stream(1, first, count, model=0, noise_var=noise_var)
+        assert ctx.last_kernel in ("clt256_s16", "generic")
+        ref = orc.clt_run(recurrences.packed(256), 1, first, count, model=0, noise_var=noise_var, want=("out16",))
+        assert np.array_equal(got, ref["out16"])
+    finally:
+        ctx.set_tuning("clt_spec_min_steps", 512)
+        ctx.set_tuning("clt_spec_max_blocks", 0)

@@ -42,8 +42,8 @@ def main():
                                   "Tbit_s": nbits / ms / 1e9, "counters": r}), flush=True)
     if "streams" in what:
         c.lutopt_load_shipped(256)
-        for name, count, bytes_per in (("clt_stream_i8", 1 << 31, 1), ("clt_stream_i16", 1 << 30, 2),
-                                       ("lutopt_stream", 1 << 26, 32)):
+        for name, count, bytes_per in (("clt_stream_i8", 1 << 33, 1), ("clt_stream_i16", 1 << 32, 2),
+                                       ("lutopt_stream", 1 << 28, 32)):
             buf = torch.empty(count * bytes_per, dtype=torch.uint8, device="cuda")
             ms = []
             for _ in range(3):
