@@ -163,7 +163,7 @@ void bbb_destroy(bbb_ctx *c)
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (int i = 0; i < 8; i++) if (c->d_scratch[i]) cudaFree(c->d_scratch[i]);
+    for (int i = 0; i < 12; i++) if (c->d_scratch[i]) cudaFree(c->d_scratch[i]);
     if (c->d_row_ptr) cudaFree(c->d_row_ptr);
     if (c->d_taps) cudaFree(c->d_taps);
     bbb_prbs_free_tables(c);
@@ -202,6 +202,8 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
     else if (!strcmp(key, "clt_spec_min_steps")) c->tune_spec_min_steps = value < 1 ? 1u : (uint32_t)value;
     else if (!strcmp(key, "clt_spec_max_blocks")) c->tune_spec_max_blocks = value < 0 ? 0u : (uint32_t)value;
     else if (!strcmp(key, "prbs_chunk_words")) c->tune_prbs_chunk_words = value < 0 ? 0u : (uint32_t)value;
+    else if (!strcmp(key, "hunt_smem_taps")) c->tune_hunt_smem_taps = (int)value;
+    else if (!strcmp(key, "hunt_slow_check")) c->tune_hunt_slow_check = value != 0;
     else if (!strcmp(key, "hunt_batch")) c->tune_hunt_batch = value < 0 ? 0u : (uint32_t)value;
     else if (!strcmp(key, "prbs_stream_reps")) c->tune_prbs_stream_reps = value < 0 ? 0u : (uint32_t)value;
     else return c->fail(BBB_EINVAL, "unknown tuning key %s", key);

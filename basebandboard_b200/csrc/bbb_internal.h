@@ -54,6 +54,8 @@ struct bbb_ctx {
     uint32_t tune_spec_max_blocks = 0;  // 0: one CTA per SM
     uint32_t tune_prbs_chunk_words = 0; // 0: automatic detector chunk length (64-bit words)
     uint32_t tune_prbs_stream_reps = 0; // 0: automatic stream-kernel repetitions per warp
+    int tune_hunt_smem_taps = 0;        // 1: never use the taps-in-registers front kernel
+    int tune_hunt_slow_check = 0;       // 1: always use the shift-and-add primitivity kernel
     uint32_t tune_hunt_batch = 0;       // 0: 2^20 candidates per rnghunt batch
     uint32_t last_rounds = 0;           // kernel rounds of the last bbb_prbs_detect
     // PRBS jump tables per k (prbs.cu), built on first use
@@ -74,8 +76,8 @@ struct bbb_ctx {
     uint16_t *d_taps = nullptr;
 
     // scratch device buffers (grown on demand)
-    void *d_scratch[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    size_t scratch_bytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    void *d_scratch[12] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t scratch_bytes[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 
     int fail(int code, const char *fmt, ...);
     int cuda_fail(cudaError_t e, const char *what);

@@ -185,7 +185,7 @@ struct HuntOut {
 // Degree / filter verdict of one candidate and, for survivors, its polynomial.
 // c: connection polynomial bits c_j (the reference's coefficient j, highest power first).
 template <int NWP>
-__device__ __noinline__ void hunt_finish(const HuntOut &o, uint32_t n, uint32_t slot, const uint32_t (&creg)[NWP],
+__device__ __forceinline__ void hunt_finish(const HuntOut &o, uint32_t n, uint32_t slot, const uint32_t (&creg)[NWP],
                                          uint32_t l)
 {
     const uint32_t pw64 = (n + 1 + 63) / 64;
@@ -223,6 +223,31 @@ __device__ __noinline__ void hunt_finish(const HuntOut &o, uint32_t n, uint32_t 
     }
 }
 
+__device__ __forceinline__ uint32_t lds_u8(uint32_t sa)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(sa));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t sa)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(sa));
+    return v;
+}
+// byte k of t (sel = 0x4440 + k); volatile so that the compiler does not hoist the 4n step-invariant
+// extractions out of the step loop and spill them
+__device__ __forceinline__ uint32_t tap_byte(uint32_t t, uint32_t sel)
+{
+    uint32_t d;
+    asm volatile("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(t), "r"(0u), "r"(sel));
+    return d;
+}
+__device__ __forceinline__ void sts_u8(uint32_t sa, uint32_t v)
+{
+    asm volatile("st.shared.u8 [%0], %1;" ::"r"(sa), "r"(v) : "memory");
+}
+
 // ---------------------------------------------------------------------------
 // front kernel for generated candidates: one thread per candidate
 // ---------------------------------------------------------------------------
@@ -232,6 +257,7 @@ struct FrontParams {
     uint32_t count;
     HuntOut out;
     uint16_t *dump_taps;   // [n][4] taps of candidate `first` (bbb_rnghunt_candidate), else null
+    uint32_t *gtaps;       // [n][count] packed taps, scratch of hunt_front_reg_kernel
 };
 
 // shared memory: state bytes xs[(n+1)][B] words, then taps[n][B] (4 x TapT per thread and row)
@@ -259,27 +285,108 @@ __global__ void hunt_front_kernel(FrontParams p)
 
     HuntBM<NWP> bm;
     bm.init();
-    const uint8_t *xb = (const uint8_t *)(xs + tid);      // byte (bit i, generation g) at xb[i*4B + g]
-    uint8_t *xw = (uint8_t *)(xs + tid);
     const uint32_t rs = 4 * B;                            // byte stride between state bits
+    constexpr uint32_t RB = 8;                            // rows per batch: all loads, then all stores
+    const uint32_t nfull = n / RB * RB;
+    const uint32_t xs_sa = (uint32_t)__cvta_generic_to_shared(xs + tid);      // shared-window byte addresses
+    const uint32_t tp_sa = (uint32_t)__cvta_generic_to_shared(taps + (size_t)tid * 4);
+    const uint32_t tps = B * 4 * (uint32_t)sizeof(TapT);                       // bytes between rows of taps
     for (uint32_t step = 0; step < 2 * n; step++) {
-        const uint32_t go = step & 3, gn = (step + 1) & 3;
-        // x' = A . x (binary_matrix.rs:53-64 / :72): row r gathers its 3-4 taps
-#pragma unroll 4
-        for (uint32_t r = 0; r < n; r++) {
-            uint32_t v;
+        const uint32_t xo = xs_sa + (step & 3), xn = xs_sa + ((step + 1) & 3);
+        // x' = A . x (binary_matrix.rs:53-64 / :72): row r gathers its 3-4 taps.  The gathers of a
+        // batch are issued before any store so that they overlap; explicit shared-memory addresses
+        // keep a gather at three instructions (byte extract, multiply-add, LDS.U8).
+        for (uint32_t r0 = 0; r0 < nfull; r0 += RB) {
+            uint32_t v[RB];
             if (sizeof(TapT) == 1) {
-                const uint32_t t4 = *(const uint32_t *)(taps + ((size_t)r * B + tid) * 4);
-                v = xb[(t4 & 0xffu) * rs + go] ^ xb[((t4 >> 8) & 0xffu) * rs + go] ^
-                    xb[((t4 >> 16) & 0xffu) * rs + go] ^ xb[(t4 >> 24) * rs + go];
+                uint32_t t4[RB];
+#pragma unroll
+                for (uint32_t k = 0; k < RB; k++) t4[k] = lds_u32(tp_sa + (r0 + k) * tps);
+#pragma unroll
+                for (uint32_t k = 0; k < RB; k++)
+                    v[k] = lds_u8(__byte_perm(t4[k], 0, 0x4440) * rs + xo) ^ lds_u8(__byte_perm(t4[k], 0, 0x4441) * rs + xo) ^
+                           lds_u8(__byte_perm(t4[k], 0, 0x4442) * rs + xo) ^ lds_u8(__byte_perm(t4[k], 0, 0x4443) * rs + xo);
             } else {
-                const uint2 t4 = *(const uint2 *)(taps + ((size_t)r * B + tid) * 4);
-                v = xb[(t4.x & 0xffffu) * rs + go] ^ xb[(t4.x >> 16) * rs + go] ^
-                    xb[(t4.y & 0xffffu) * rs + go] ^ xb[(t4.y >> 16) * rs + go];
+                uint32_t ta[RB], tb[RB];
+#pragma unroll
+                for (uint32_t k = 0; k < RB; k++) {
+                    ta[k] = lds_u32(tp_sa + (r0 + k) * tps);
+                    tb[k] = lds_u32(tp_sa + (r0 + k) * tps + 4);
+                }
+#pragma unroll
+                for (uint32_t k = 0; k < RB; k++)
+                    v[k] = lds_u8((ta[k] & 0xffffu) * rs + xo) ^ lds_u8((ta[k] >> 16) * rs + xo) ^
+                           lds_u8((tb[k] & 0xffffu) * rs + xo) ^ lds_u8((tb[k] >> 16) * rs + xo);
             }
-            xw[r * rs + gn] = (uint8_t)v;
+#pragma unroll
+            for (uint32_t k = 0; k < RB; k++) sts_u8(xn + (r0 + k) * rs, v[k]);
         }
-        bm.push(xb[gn]);                                  // x[0] after the step (binary_matrix.rs:73)
+        for (uint32_t r = nfull; r < n; r++) {
+            uint32_t c[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) c[k] = taps[((size_t)r * B + tid) * 4 + k];
+            const uint32_t v = lds_u8(c[0] * rs + xo) ^ lds_u8(c[1] * rs + xo) ^ lds_u8(c[2] * rs + xo) ^ lds_u8(c[3] * rs + xo);
+            sts_u8(xn + r * rs, v);
+        }
+        bm.push(lds_u8(xn));                              // x[0] after the step (binary_matrix.rs:73)
+    }
+    hunt_finish<NWP>(p.out, n, slot, bm.c, bm.l);
+}
+
+// ---------------------------------------------------------------------------
+// front kernel with the tap lists in REGISTERS (n <= 32*NW <= 192): the row loop is fully unrolled,
+// row r's four column indices are the bytes of register tp[r]; shared memory holds only the state
+// bytes, so twice as many warps fit on an SM and a row costs no tap load.  The generator hands the
+// taps over through a global scratch array (written and read once, coalesced).
+// ---------------------------------------------------------------------------
+template <int NW>
+__global__ void __launch_bounds__(32, 8)
+hunt_front_reg_kernel(FrontParams p)
+{
+    constexpr int NWP = NW + 1;
+    constexpr uint32_t NR = 32 * NW;
+    extern __shared__ uint32_t hsm[];
+    const uint32_t B = 32, tid = threadIdx.x, n = p.n;
+    const uint32_t slot = blockIdx.x * B + tid;
+    if (slot >= p.count) return;
+    const uint64_t cand = p.first + (uint64_t)slot * p.stride;
+    {
+        uint32_t acc = 0;
+        hunt_generate<NW>(n, p.seed, cand, [&](uint32_t row, uint32_t k, uint32_t col) {
+            acc |= col << (8 * k);
+            if (k == 3) { p.gtaps[(size_t)row * p.count + slot] = acc; acc = 0; }
+        });
+    }
+    uint32_t tp[NR];
+#pragma unroll
+    for (uint32_t r = 0; r < NR; r++) tp[r] = r < n ? p.gtaps[(size_t)r * p.count + slot] : 0u;
+
+    uint32_t *xs = hsm;
+    for (uint32_t i = 0; i < n; i++) xs[i * B + tid] = 1u;     // b = all ones (rnghunt.rs:28)
+    xs[n * B + tid] = 0u;                                       // row n: what empty tap slots read
+    const uint32_t xs_sa = (uint32_t)__cvta_generic_to_shared(xs + tid);
+    constexpr uint32_t rs = 4 * 32;
+    HuntBM<NWP> bm;
+    bm.init();
+#pragma unroll 1
+    for (uint32_t step = 0; step < 2 * n; step++) {
+        const uint32_t xo = xs_sa + (step & 3), xn = xs_sa + ((step + 1) & 3);
+#pragma unroll
+        for (uint32_t r0 = 0; r0 < NR; r0 += 8) {
+            if (r0 < n) {                                       // warp-uniform
+                uint32_t v[8];
+#pragma unroll
+                for (uint32_t k = 0; k < 8; k++)
+                    v[k] = lds_u8(tap_byte(tp[r0 + k], 0x4440u) * rs + xo) ^
+                           lds_u8(tap_byte(tp[r0 + k], 0x4441u) * rs + xo) ^
+                           lds_u8(tap_byte(tp[r0 + k], 0x4442u) * rs + xo) ^
+                           lds_u8(tap_byte(tp[r0 + k], 0x4443u) * rs + xo);
+#pragma unroll
+                for (uint32_t k = 0; k < 8; k++)
+                    if (r0 + k < n) sts_u8(xn + (r0 + k) * rs, v[k]);
+            }
+        }
+        bm.push(lds_u8(xn));
     }
     hunt_finish<NWP>(p.out, n, slot, bm.c, bm.l);
 }
@@ -416,6 +523,91 @@ hunt_check_kernel(CheckParams q)
     if (rest == 0) atomicOr(&q.result[sidx], 1u << (ei > 31 ? 31 : ei));
 }
 
+// The same test for n = 32*NW with a per-polynomial table R_j = x^(n+j) mod p, j < 32, in shared
+// memory (word [j][w][thread]): squaring = bit spread + folding the high half 32 bits at a time
+// (one table row per set bit), about 4x fewer instructions than shift-and-add.
+__device__ __forceinline__ uint32_t spread16(uint32_t x)   // bit i of the low half -> bit 2i
+{
+    x &= 0xffffu;
+    x = (x | (x << 8)) & 0x00ff00ffu;
+    x = (x | (x << 4)) & 0x0f0f0f0fu;
+    x = (x | (x << 2)) & 0x33333333u;
+    x = (x | (x << 1)) & 0x55555555u;
+    return x;
+}
+
+template <int NW>
+__global__ void __launch_bounds__(64)
+hunt_check32_kernel(CheckParams q, uint32_t stride)
+{
+    extern __shared__ uint32_t rsm[];
+    const uint32_t B = blockDim.x, tid = threadIdx.x;
+    const uint32_t item = blockIdx.x * B + tid;
+    if (item >= q.nitems) return;
+    const uint32_t pi = item / q.nexp, ei = q.exp_first + item % q.nexp;
+    const uint32_t sidx = q.poly_index ? q.poly_index[pi] : pi;
+    uint32_t *const R = rsm + tid;
+    uint32_t pl[NW], r[NW];                        // p without its leading term = x^n mod p
+#pragma unroll
+    for (int w = 0; w < NW; w++) pl[w] = q.polys[(size_t)sidx * stride + w];
+    {
+        uint32_t t[NW];
+#pragma unroll
+        for (int w = 0; w < NW; w++) t[w] = pl[w];
+        for (uint32_t j = 0; j < 32; j++) {
+#pragma unroll
+            for (int w = 0; w < NW; w++) R[(j * NW + w) * B] = t[w];
+            const uint32_t m = 0u - (t[NW - 1] >> 31);
+#pragma unroll
+            for (int w = NW - 1; w > 0; w--) t[w] = ((t[w] << 1) | (t[w - 1] >> 31)) ^ (pl[w] & m);
+            t[0] = (t[0] << 1) ^ (pl[0] & m);
+        }
+    }
+#pragma unroll
+    for (int w = 0; w < NW; w++) r[w] = 0;
+    r[0] = 1;
+    const uint64_t *e = q.exp_words + q.exp_off[ei];
+    const uint32_t ew = q.exp_off[ei + 1] - q.exp_off[ei];
+    bool started = false;
+    for (uint32_t wi = 0; wi < ew; wi++) {
+        const uint64_t word = e[wi];
+        for (int b = 63; b >= 0; b--) {
+            const uint32_t bit = (uint32_t)(word >> b) & 1u;
+            if (!started) {
+                if (!bit) continue;
+                started = true;
+            } else {
+                uint32_t V[2 * NW];
+#pragma unroll
+                for (int w = 0; w < NW; w++) { V[2 * w] = spread16(r[w]); V[2 * w + 1] = spread16(r[w] >> 16); }
+#pragma unroll
+                for (int qq = NW - 1; qq >= 0; qq--) {
+                    uint32_t chunk = V[NW + qq];               // coefficients of x^(n+32qq+j)
+                    while (chunk) {
+                        const uint32_t j = __ffs(chunk) - 1;
+                        chunk &= chunk - 1;
+                        const uint32_t *Rj = R + (size_t)j * NW * B;
+#pragma unroll
+                        for (int w = 0; w < NW; w++) V[qq + w] ^= Rj[w * B];
+                    }
+                }
+#pragma unroll
+                for (int w = 0; w < NW; w++) r[w] = V[w];
+            }
+            if (bit) {                                         // times x
+                const uint32_t m = 0u - (r[NW - 1] >> 31);
+#pragma unroll
+                for (int w = NW - 1; w > 0; w--) r[w] = ((r[w] << 1) | (r[w - 1] >> 31)) ^ (pl[w] & m);
+                r[0] = (r[0] << 1) ^ (pl[0] & m);
+            }
+        }
+    }
+    uint32_t rest = r[0] ^ 1u;
+#pragma unroll
+    for (int w = 1; w < NW; w++) rest |= r[w];
+    if (rest == 0) atomicOr(&q.result[sidx], 1u << (ei > 31 ? 31 : ei));
+}
+
 // survivors whose x^(2^n-1) == 1 go on to the cofactor tests (binary_polynomial.rs:198-208)
 __global__ void hunt_compact_kernel(const uint32_t *__restrict__ result, uint32_t nsurv, uint32_t *pass_count,
                                     uint32_t *pass_index)
@@ -507,6 +699,27 @@ static int hunt_buffers(bbb_ctx *c, uint32_t n, uint32_t cap, uint32_t nwp, Hunt
 static int launch_check(bbb_ctx *c, uint32_t nwp, const CheckParams &q)
 {
     if (!q.nitems) return BBB_OK;
+    if (q.n % 32 == 0 && !c->tune_hunt_slow_check) {
+        const uint32_t nw = q.n / 32, B = 64;
+        const size_t smem = (size_t)32 * nw * B * 4;
+        const uint32_t blocks = (q.nitems + B - 1) / B;
+#define CHECK32_CASE(N)                                                                                        \
+    case N:                                                                                                    \
+        BBB_CUDA(c, cudaFuncSetAttribute(hunt_check32_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                         (int)smem));                                                          \
+        hunt_check32_kernel<N><<<blocks, B, smem, c->stream>>>(q, nwp);                                        \
+        break
+        switch (nw) {
+            CHECK32_CASE(1); CHECK32_CASE(2); CHECK32_CASE(3); CHECK32_CASE(4); CHECK32_CASE(5); CHECK32_CASE(6);
+            CHECK32_CASE(7); CHECK32_CASE(8); CHECK32_CASE(9); CHECK32_CASE(10); CHECK32_CASE(11); CHECK32_CASE(12);
+            CHECK32_CASE(13); CHECK32_CASE(14); CHECK32_CASE(15); CHECK32_CASE(16);
+        default: return c->fail(BBB_EINVAL, "bad n");
+        }
+#undef CHECK32_CASE
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        return BBB_OK;
+    }
     const uint32_t blocks = (q.nitems + 127) / 128;
 #define CHECK_CASE(N) case N: hunt_check_kernel<N><<<blocks, 128, 0, c->stream>>>(q); break
     switch (nwp) {
@@ -570,6 +783,27 @@ static int hunt_back_end(bbb_ctx *c, uint32_t n, uint32_t count, uint32_t nwp, H
 static int launch_front(bbb_ctx *c, const FrontParams &p)
 {
     const uint32_t n = p.n, nw = (n + 31) / 32, B = 32;
+    // taps in registers pay off once the shared-memory kernel is down to a few warps per SM (n > 128);
+    // "hunt_smem_taps" = 2 forces the register kernel for every n <= 192 (tests)
+    if (p.gtaps && nw <= 6 && (nw >= 5 ? c->tune_hunt_smem_taps != 1 : c->tune_hunt_smem_taps == 2)) {
+        const size_t smem = (size_t)B * (n + 1) * 4;
+        const uint32_t blocks = (p.count + B - 1) / B;
+#define FRONT_REG_CASE(NW)                                                                                \
+    case NW:                                                                                              \
+        BBB_CUDA(c, cudaFuncSetAttribute(hunt_front_reg_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                         (int)smem));                                                     \
+        hunt_front_reg_kernel<NW><<<blocks, B, smem, c->stream>>>(p);                                     \
+        break
+        switch (nw) {
+            FRONT_REG_CASE(1); FRONT_REG_CASE(2); FRONT_REG_CASE(3); FRONT_REG_CASE(4); FRONT_REG_CASE(5);
+            FRONT_REG_CASE(6);
+        default: break;
+        }
+#undef FRONT_REG_CASE
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        return BBB_OK;
+    }
     const bool wide = n > 255;                         // the "no tap" index n must fit the tap type
     const size_t smem = (size_t)B * ((n + 1) * 4 + (size_t)n * 4 * (wide ? 2 : 1));
     const uint32_t blocks = (p.count + B - 1) / B;
@@ -634,6 +868,8 @@ int bbb_rnghunt_sweep(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uin
         p.n = n; p.seed = seed; p.first = first + done * stride; p.stride = stride; p.count = nb;
         p.out.stage = b.stage; p.out.surv_count = b.counters; p.out.surv_cand = b.surv_cand;
         p.out.surv_poly = b.surv_poly; p.out.poly_out = nullptr; p.dump_taps = nullptr;
+        p.gtaps = n <= 192 ? (uint32_t *)c->scratch(8, (size_t)n * cap * 4) : nullptr;
+        if (n <= 192 && !p.gtaps) return BBB_ECUDA;
         rc = launch_front(c, p);
         if (rc) return rc;
         rc = hunt_back_end(c, n, nb, nwp, b, hit_slots);

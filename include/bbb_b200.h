@@ -84,7 +84,8 @@ uint64_t bbb_last_d2h_bytes(const bbb_ctx *ctx);
 uint32_t bbb_last_rounds(const bbb_ctx *ctx);
 /* Tuning knobs, for tests and experiments (results never depend on them):
  *   "clt_no_spec" (0/1), "clt_spec_min_steps", "clt_spec_max_blocks",
- *   "prbs_chunk_words", "prbs_stream_reps". */
+ *   "prbs_chunk_words", "prbs_stream_reps", "hunt_batch", "hunt_slow_check" (0/1),
+ *   "hunt_smem_taps" (0 auto, 1 shared-memory taps, 2 register taps). */
 int  bbb_set_tuning(bbb_ctx *ctx, const char *key, int64_t value);
 /* Region timer: CUDA events on the ctx's stream around any number of calls.
  * bbb_timer_stop waits for the stream and returns the device time in ms. */

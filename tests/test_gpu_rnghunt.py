@@ -150,3 +150,31 @@ def test_bad_arguments(ctx):
         ctx.rnghunt_sweep(1024, 1, 0, 10)
     with pytest.raises(lib.BBBError):
         ctx.rnghunt_sweep(32, 1, 0, 10, stride=0)
+
+
+@pytest.mark.parametrize("n", [32, 64, 192])
+def test_table_and_shift_add_primitivity_kernels_agree(ctx, n):
+    """hunt_check32_kernel (table-folded squaring, n % 32 == 0) vs hunt_check_kernel (shift-and-add)."""
+    count = 20000 if n < 192 else 6000
+    fast = ctx.rnghunt_sweep(n, 11, 0, count, k=32, want_stages=True)
+    ctx.set_tuning("hunt_slow_check", 1)
+    try:
+        slow = ctx.rnghunt_sweep(n, 11, 0, count, k=32, want_stages=True)
+    finally:
+        ctx.set_tuning("hunt_slow_check", 0)
+    assert np.array_equal(fast["stages"], slow["stages"]) and fast["best"] == slow["best"]
+    assert fast["stage_counts"][STAGE_ORDER] > 0
+
+
+@pytest.mark.parametrize("n", [16, 33, 100, 192])
+def test_register_and_shared_tap_front_kernels_agree(ctx, n):
+    """hunt_front_reg_kernel (taps in registers, n <= 192) vs hunt_front_kernel (taps in shared memory)."""
+    count = 5000
+    ctx.set_tuning("hunt_smem_taps", 2)       # register kernel for every n <= 192
+    a = ctx.rnghunt_sweep(n, 21, 7, count, k=8, want_stages=True)
+    ctx.set_tuning("hunt_smem_taps", 1)
+    try:
+        b = ctx.rnghunt_sweep(n, 21, 7, count, k=8, want_stages=True)
+    finally:
+        ctx.set_tuning("hunt_smem_taps", 0)
+    assert np.array_equal(a["stages"], b["stages"]) and a["best"] == b["best"]
