@@ -199,6 +199,7 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
 {
     if (!c || !key) return BBB_EINVAL;
     if (!strcmp(key, "clt_no_spec")) c->tune_no_spec = value != 0;
+    else if (!strcmp(key, "clt_spec_variant")) c->tune_spec_variant = value == 1 ? 1 : 2;
     else if (!strcmp(key, "clt_spec_min_steps")) c->tune_spec_min_steps = value < 1 ? 1u : (uint32_t)value;
     else if (!strcmp(key, "clt_spec_max_blocks")) c->tune_spec_max_blocks = value < 0 ? 0u : (uint32_t)value;
     else if (!strcmp(key, "prbs_chunk_words")) c->tune_prbs_chunk_words = value < 0 ? 0u : (uint32_t)value;

@@ -50,6 +50,7 @@ struct bbb_ctx {
     int shipped = 0;              // n of the shipped matrix this equals, else 0
     // tuning knobs (bbb_set_tuning): tests use them to force a code path
     int tune_no_spec = 0;               // 1: never use the specialised n256 kernel
+    int tune_spec_variant = 2;          // fused n256 kernel: 1 two-pass (clt256_gen.inc), 2 one-pass (clt256_v2_gen.inc)
     uint32_t tune_spec_min_steps = 512; // fewest clocks per stream worth a specialised launch
     uint32_t tune_spec_max_blocks = 0;  // 0: one CTA per SM
     uint32_t tune_prbs_chunk_words = 0; // 0: automatic detector chunk length (64-bit words)

@@ -103,6 +103,99 @@ clt256_hist_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, 
         if (slow[i]) atomicAdd(&hist[i], (unsigned long long)slow[i]);
 }
 
+// ===========================================================================
+// one-pass variant (tools/gen_clt256_v2.py): the old state is read once per clock, rows are folded
+// as their taps arrive, new planes are stored in place.  State: slot p of thread tid at word
+// p*128 + tid (conflict-free LDS.32/STS.32), 1.0 buffer = 128 KB per CTA.  The private histogram is
+// reached through explicit shared-space addresses in volatile asm: ordered among themselves, and
+// invisible to the compiler's alias analysis of the state words (which sees constant offsets only).
+// ===========================================================================
+#define CLT256V2_B 128
+#define CLT256V2_STATE_BYTES (256 * CLT256V2_B * 4)
+#define CLT256V2_SLOW_WORDS 264                       // 257 bins + [257] = slow-path samples (cancel bin 0)
+#define CLT256V2_SMEM (CLT256V2_STATE_BYTES + CLT256_FAST_BYTES + CLT256V2_SLOW_WORDS * 4)
+
+#define CLT256V2_SECTION_PERM
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_PERM
+
+static __device__ __noinline__ void clt256v2_slow(uint32_t p0, uint32_t p1, uint32_t p2, uint32_t p3, uint32_t p4,
+                                                  uint32_t p5, uint32_t p6, uint32_t p7, uint32_t p8, uint32_t outm,
+                                                  uint32_t model, uint32_t *slow)
+{
+    while (outm) {
+        const uint32_t j = __ffs(outm) - 1;
+        outm &= outm - 1;
+        uint32_t v = ((p0 >> j) & 1u) | (((p1 >> j) & 1u) << 1) | (((p2 >> j) & 1u) << 2) | (((p3 >> j) & 1u) << 3) |
+                     (((p4 >> j) & 1u) << 4) | (((p5 >> j) & 1u) << 5) | (((p6 >> j) & 1u) << 6) |
+                     (((p7 >> j) & 1u) << 7) | (((p8 >> j) & 1u) << 8);
+        if (model == BBB_MODEL_GATEWARE) v &= 255u;   // Signal((logn, True)), rng.py:78
+        atomicAdd(&slow[v], 1u);
+        atomicAdd(&slow[257], 1u);                    // its masked index lands in private bin 0: cancelled at the end
+    }
+}
+
+#define CLT256V2_AFTER_COUNT(p0, p1, p2, p3, p4, p5, p6, p7, p8, inr) \
+    if ((inr) != 0xffffffffu) clt256v2_slow(p0, p1, p2, p3, p4, p5, p6, p7, p8, ~(inr), model, slow);
+
+// byte m of z = 6-bit bin of one sample; bin b of this thread's column is 128 bytes * b above hp
+#define CLT256V2_RMW_LD(nm, z, m)                                                                        \
+    uint32_t a##nm, h##nm;                                                                               \
+    asm volatile("{\n\t.reg .b32 t;\n\tprmt.b32 t, %2, 0, 0x444" #m ";\n\tmad.lo.u32 %0, t, 128, %3;\n\t" \
+                 "ld.shared.u32 %1, [%0];\n\t}"                                                          \
+                 : "=r"(a##nm), "=r"(h##nm) : "r"(z), "r"(hp));
+#define CLT256V2_RMW_ST(nm) asm volatile("st.shared.u32 [%0], %1;" ::"r"(a##nm), "r"(h##nm + 1u));
+
+__global__ void __launch_bounds__(CLT256V2_B, 1)
+clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t model,
+                    unsigned long long *__restrict__ hist)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+    char *smb = (char *)smem4;
+    uint32_t *fast = (uint32_t *)(smb + CLT256V2_STATE_BYTES);
+    uint32_t *slow = (uint32_t *)(smb + CLT256V2_STATE_BYTES + CLT256_FAST_BYTES);
+    for (uint32_t i = tid; i < CLT256_FAST_BYTES / 4; i += CLT256V2_B) fast[i] = 0;
+    for (uint32_t i = tid; i < CLT256V2_SLOW_WORDS; i += CLT256V2_B) slow[i] = 0;
+    uint32_t *const st = (uint32_t *)smem4 + tid;
+    for (uint32_t p = 0; p < 256; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_PERM[p] * T + t];
+    __syncthreads();
+    const uint32_t hp = (uint32_t)__cvta_generic_to_shared(fast + (tid >> 5) * 2048 + (tid & 31));
+    uint32_t z0 = 0, z1 = 0, z2 = 0, z3 = 0, z4 = 0, z5 = 0, z6 = 0, z7 = 0;
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_BODY
+    }
+    __syncthreads();
+    // the last clock's samples; the first clock ran 32 updates of bin 0 on the zero-initialised z words
+    {
+        uint32_t *col = fast + (tid >> 5) * 2048 + (tid & 31);
+        const uint32_t zz[8] = {z0, z1, z2, z3, z4, z5, z6, z7};
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+#pragma unroll
+            for (int m = 0; m < 4; m++) col[((zz[k] >> (8 * m)) & 0x3fu) * 32] += 1u;
+        col[0] -= 32u;
+    }
+    __syncthreads();
+    if (tid < 64) {
+        unsigned long long s = 0;
+        for (uint32_t w = 0; w < 4; w++)
+            for (uint32_t l = 0; l < 32; l++) s += fast[w * 2048 + tid * 32 + ((l + tid) & 31)];
+        if (tid == 0) s -= slow[257];
+        if (s) atomicAdd(&hist[96 + tid], s);
+    }
+    for (uint32_t i = tid; i < 257; i += CLT256V2_B)
+        if (slow[i]) atomicAdd(&hist[i], (unsigned long long)slow[i]);
+}
+
 // Streams one CTA carries, and whether the loaded recurrence has a specialised kernel.
 int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only)
 {
@@ -117,10 +210,17 @@ int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model,
 {
     static_assert(CLT256_SMEM <= 227 * 1024, "shared memory budget");
     BBB_CUDA(c, cudaFuncSetAttribute(clt256_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256_SMEM));
-    clt256_hist_kernel<<<blocks, CLT256_B, CLT256_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, model, hist);
+    if (c->tune_spec_variant == 1) {
+        clt256_hist_kernel<<<blocks, CLT256_B, CLT256_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, model, hist);
+        c->last_kernel = "clt256_fused";
+    } else {
+        static_assert(CLT256V2_SMEM <= 227 * 1024, "shared memory budget");
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_hist2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2_SMEM));
+        clt256_hist2_kernel<<<blocks, CLT256V2_B, CLT256V2_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, model, hist);
+        c->last_kernel = "clt256_fused2";
+    }
     c->last_launches++;
     BBB_CUDA(c, cudaGetLastError());
-    c->last_kernel = "clt256_fused";
     return BBB_OK;
 }
 

@@ -290,6 +290,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample length")
     ap.add_argument("--ref-step-seconds", type=float, default=4.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tune", action="append", default=[], metavar="KEY=VALUE",
+                    help="bbb_set_tuning knob (experiments only), e.g. clt_spec_variant=1")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -312,6 +314,9 @@ def main():
             os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = lib.Context(local_rank)
+    for kv in args.tune:
+        key, _, val = kv.partition("=")
+        ctx.set_tuning(key, int(val))
     if args.workload != "clt_fused":
         return run_secondary(args, ctx, rank, world, local_rank)
     ctx.lutopt_load_shipped(N_STATE)

@@ -144,20 +144,26 @@ def test_stats_match_numpy(ctx):
 
 
 # ---- the specialised n256 kernel (clt_spec.cu) -------------------------------------------------
+FUSED_NAME = {1: "clt256_fused", 2: "clt256_fused2"}
+
+
+@pytest.mark.parametrize("variant", [1, 2])
 @pytest.mark.parametrize("model", [0, 1])
 @pytest.mark.parametrize("blocks,min_steps,count", [(1, 40, 4096 * 57 + 123), (3, 33, 3 * 4096 * 70 + 4099),
                                                    (0, 16, 5_000_011)])
-def test_spec256_matches_oracle(ctx, orc, model, blocks, min_steps, count):
-    """clt256_fused (straight-line bit-sliced kernel) + generic tail == oracle, both models; the
-    count is large enough that popcounts outside [96,160) occur (the atomic slow path)."""
+def test_spec256_matches_oracle(ctx, orc, model, blocks, min_steps, count, variant):
+    """clt256_fused / clt256_fused2 (straight-line bit-sliced kernels, two-pass and one-pass) + generic
+    tail == oracle, both models; the count is large enough that popcounts outside [96,160) occur
+    (the atomic slow path)."""
     ctx.lutopt_load_shipped(256)
+    ctx.set_tuning("clt_spec_variant", variant)
     ctx.set_tuning("clt_spec_min_steps", min_steps)
     ctx.set_tuning("clt_spec_max_blocks", blocks)
     try:
         init = 1 if blocks != 3 else (0x5DEECE66D << 190) | 0xB
         first = 0 if blocks != 3 else (1 << 41) + 9
         h, s, ss = ctx.clt_hist(init, first, count, model)
-        assert ctx.last_kernel == "clt256_fused" or count < 4096 * min_steps
+        assert ctx.last_kernel == FUSED_NAME[variant] or count < 4096 * min_steps
         oh, os_, oss = _oracle_hist(orc, 256, init, first, count, model)
         assert np.array_equal(h, oh)
         assert (s, ss) == (os_, oss)
@@ -166,13 +172,20 @@ def test_spec256_matches_oracle(ctx, orc, model, blocks, min_steps, count):
     finally:
         ctx.set_tuning("clt_spec_min_steps", 512)
         ctx.set_tuning("clt_spec_max_blocks", 0)
+        ctx.set_tuning("clt_spec_variant", 2)
 
 
 def test_spec256_equals_generic_large(ctx):
-    """2^31 samples: specialised kernel == data-driven kernel (bit-exact histograms and moments)."""
+    """2^31 samples: both specialised kernels == data-driven kernel (bit-exact histograms and moments)."""
     ctx.lutopt_load_shipped(256)
     a = ctx.clt_hist(1, 12345, 1 << 31, 0)
-    assert ctx.last_kernel == "clt256_fused"
+    assert ctx.last_kernel == "clt256_fused2"
+    ctx.set_tuning("clt_spec_variant", 1)
+    try:
+        a1 = ctx.clt_hist(1, 12345, 1 << 31, 0)
+        assert ctx.last_kernel == "clt256_fused"
+    finally:
+        ctx.set_tuning("clt_spec_variant", 2)
     ctx.set_tuning("clt_no_spec", 1)
     try:
         b = ctx.clt_hist(1, 12345, 1 << 31, 0)
@@ -180,6 +193,7 @@ def test_spec256_equals_generic_large(ctx):
     finally:
         ctx.set_tuning("clt_no_spec", 0)
     assert np.array_equal(a[0], b[0]) and a[1:] == b[1:]
+    assert np.array_equal(a1[0], b[0]) and a1[1:] == b[1:]
     assert int(a[0].sum()) == 1 << 31
 
 
