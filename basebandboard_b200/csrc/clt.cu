@@ -236,6 +236,7 @@ static int launch_seed(bbb_ctx *c, const uint32_t *dJ, const SeedStart &xs, uint
 
 // clt_spec.cu
 int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only);
+int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c);
 int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model, const uint32_t *planes,
                         unsigned long long *hist);
 int bbb_clt_spec_stream_ok(const bbb_ctx *c, int kind);
@@ -348,7 +349,8 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
 
         // ---- specialised kernel: `blocks` CTAs x spb streams x L clocks, one wave ----
         if (spb && ((kind != 1 && kind != 3) || (done & 7) == 0)) {
-            const uint64_t max_blocks = c->tune_spec_max_blocks ? c->tune_spec_max_blocks : (uint64_t)c->sm_count;
+            const uint64_t max_blocks = c->tune_spec_max_blocks ? c->tune_spec_max_blocks
+                                        : (uint64_t)c->sm_count * (kind == 0 ? bbb_clt_spec_blocks_per_sm(c) : 1);
             // fewest clocks per stream worth a launch (the stream kernels amortise their seeding sooner)
             const uint64_t min_steps = kind > 0 ? (c->tune_spec_min_steps / 4 > 8 ? c->tune_spec_min_steps / 4 : 8)
                                                 : c->tune_spec_min_steps;

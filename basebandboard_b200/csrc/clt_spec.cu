@@ -111,9 +111,10 @@ clt256_hist_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, 
 // invisible to the compiler's alias analysis of the state words (which sees constant offsets only).
 // ===========================================================================
 #define CLT256V2_B 128
-#define CLT256V2_STATE_BYTES (256 * CLT256V2_B * 4)
+#define CLT256V2_STATE_BYTES (CLT256V2_NSLOTS * CLT256V2_B * 4)
 #define CLT256V2_SLOW_WORDS 264                       // 257 bins + [257] = slow-path samples (cancel bin 0)
 #define CLT256V2_SMEM (CLT256V2_STATE_BYTES + CLT256_FAST_BYTES + CLT256V2_SLOW_WORDS * 4)
+#define CLT256V2_CTAS_PER_SM 2                        // 2 x (state + bins + 1 KB) <= 228 KB, 2 x 128 x 254 registers
 
 #define CLT256V2_SECTION_PERM
 #include "clt256_v2_gen.inc"
@@ -144,10 +145,11 @@ static __device__ __noinline__ void clt256v2_slow(uint32_t p0, uint32_t p1, uint
     asm volatile("{\n\t.reg .b32 t;\n\tprmt.b32 t, %2, 0, 0x444" #m ";\n\tmad.lo.u32 %0, t, 128, %3;\n\t" \
                  "ld.shared.u32 %1, [%0];\n\t}"                                                          \
                  : "=r"(a##nm), "=r"(h##nm) : "r"(z), "r"(hp));
-#define CLT256V2_RMW_ST(nm) asm volatile("st.shared.u32 [%0], %1;" ::"r"(a##nm), "r"(h##nm + 1u));
+#define CLT256V2_RMW_ST(nm)                                                                              \
+    asm volatile("{\n\t.reg .b32 t;\n\tmad.lo.u32 t, %1, %2, %2;\n\tst.shared.u32 [%0], t;\n\t}" ::"r"(a##nm), "r"(h##nm), "r"(one));
 
-__global__ void __launch_bounds__(CLT256V2_B, 1)
-clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t model,
+__global__ void __launch_bounds__(CLT256V2_B, CLT256V2_CTAS_PER_SM)
+clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t model, uint32_t one,
                     unsigned long long *__restrict__ hist)
 {
     extern __shared__ uint4 smem4[];
@@ -159,14 +161,16 @@ clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
     for (uint32_t i = tid; i < CLT256_FAST_BYTES / 4; i += CLT256V2_B) fast[i] = 0;
     for (uint32_t i = tid; i < CLT256V2_SLOW_WORDS; i += CLT256V2_B) slow[i] = 0;
     uint32_t *const st = (uint32_t *)smem4 + tid;
-    for (uint32_t p = 0; p < 256; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_PERM[p] * T + t];
+    for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
     __syncthreads();
     const uint32_t hp = (uint32_t)__cvta_generic_to_shared(fast + (tid >> 5) * 2048 + (tid & 31));
-    uint32_t z0 = 0, z1 = 0, z2 = 0, z3 = 0, z4 = 0, z5 = 0, z6 = 0, z7 = 0;
 #define CLT256V2_SECTION_RESIDENT_DECL
 #include "clt256_v2_gen.inc"
 #undef CLT256V2_SECTION_RESIDENT_DECL
 
+    // Software-pipelined: iteration `it` reads the state before clock `it`, feeds it to the popcount
+    // network and clocks the recurrence; the last levels of that network, the range test and the
+    // un-slicing of clock it-1 (carried in the k<w>_<i> planes) are interleaved with its first steps.
 #pragma unroll 1
     for (uint32_t it = 0; it < L; it++) {
 #define CLT256V2_SECTION_BODY
@@ -174,15 +178,18 @@ clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
 #undef CLT256V2_SECTION_BODY
     }
     __syncthreads();
-    // the last clock's samples; the first clock ran 32 updates of bin 0 on the zero-initialised z words
     {
+        // the last clock's samples; the carried planes started as 32 fake samples of popcount 128 (bin 32)
+#define CLT256V2_SECTION_TAIL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_TAIL
         uint32_t *col = fast + (tid >> 5) * 2048 + (tid & 31);
         const uint32_t zz[8] = {z0, z1, z2, z3, z4, z5, z6, z7};
 #pragma unroll
         for (int k = 0; k < 8; k++)
 #pragma unroll
             for (int m = 0; m < 4; m++) col[((zz[k] >> (8 * m)) & 0x3fu) * 32] += 1u;
-        col[0] -= 32u;
+        col[32 * 32] -= 32u;
     }
     __syncthreads();
     if (tid < 64) {
@@ -195,6 +202,9 @@ clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
     for (uint32_t i = tid; i < 257; i += CLT256V2_B)
         if (slow[i]) atomicAdd(&hist[i], (unsigned long long)slow[i]);
 }
+
+// CTAs of the fused kernel one SM holds at a time
+int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c) { return c->tune_spec_variant == 1 ? 1 : CLT256V2_CTAS_PER_SM; }
 
 // Streams one CTA carries, and whether the loaded recurrence has a specialised kernel.
 int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only)
@@ -214,9 +224,10 @@ int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model,
         clt256_hist_kernel<<<blocks, CLT256_B, CLT256_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, model, hist);
         c->last_kernel = "clt256_fused";
     } else {
-        static_assert(CLT256V2_SMEM <= 227 * 1024, "shared memory budget");
+        static_assert(CLT256V2_CTAS_PER_SM * (CLT256V2_SMEM + 1024) <= 228 * 1024, "shared memory budget");
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_hist2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2_SMEM));
-        clt256_hist2_kernel<<<blocks, CLT256V2_B, CLT256V2_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, model, hist);
+        // `one`: the +1 of a bin update as h * one + one keeps it on the FMA pipe (the ALU pipe is the bound)
+        clt256_hist2_kernel<<<blocks, CLT256V2_B, CLT256V2_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, model, 1u, hist);
         c->last_kernel = "clt256_fused2";
     }
     c->last_launches++;

@@ -12,7 +12,8 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
-SO_PATH = os.path.join(_HERE, "libbbb_b200.so")
+# BBB_B200_LIB: kernel experiments only (another build of the same library, e.g. build/variants/*.so)
+SO_PATH = os.environ.get("BBB_B200_LIB") or os.path.join(_HERE, "libbbb_b200.so")
 
 MODEL_GATEWARE, MODEL_NUMPY = 0, 1
 STAGE_NAMES = ("degree", "filter", "order", "factor", "primitive")

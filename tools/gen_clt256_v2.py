@@ -27,7 +27,9 @@ N = 256
 LEAD = int(os.environ.get("CLT256V2_LEAD", "6"))          # loads are issued this many steps ahead
 ITERS = int(os.environ.get("CLT256V2_ITERS", "12000000"))
 SEED = int(os.environ.get("CLT256V2_SEED", "1"))
-NRES = int(os.environ.get("CLT256V2_RESIDENT", "0"))      # planes kept in registers across clocks
+NRES = int(os.environ.get("CLT256V2_RESIDENT", "0"))      # most planes kept in registers across clocks
+RES_BUDGET = int(os.environ.get("CLT256V2_RES_BUDGET", "132"))   # modelled live values allowed with them
+POS_FILE = os.environ.get("CLT256V2_POS")                 # reuse a load order (one integer per line)
 
 
 def run_annealer(rows):
@@ -42,38 +44,118 @@ def run_annealer(rows):
     return pos
 
 
-def pick_residents(rows, pos, nres):
-    """Planes whose register life across the loop edge is shortest: finished at `done`, last raw use
-    in the next clock at `death` -> wrap length (N - done) + death."""
+def pick_residents(rows, pos, nres, budget):
+    """Planes that stay in registers across the loop edge instead of going through shared memory.
+    Plane b is finished at `done` and last needed in raw form at `death` of the next clock; it is
+    eligible when done > death (the old value is dead before the new one exists) and costs one
+    register over [done, N) and [0, pos[b]).  Greedy by shortest wrap, while the modelled live count
+    stays within `budget`."""
     if nres <= 0:
         return set()
+    import numpy as np
     times = clt256_sched.row_times(rows, pos)
+    perm = [0] * N
+    for b, p in enumerate(pos):
+        perm[p] = b
     death = {b: pos[b] for b in range(N)}
     for r in range(N):
         ts = times[r]
         fold = ts[2] if len(ts) >= 3 else ts[-1]
-        for b in rows[r]:
-            if pos[b] <= fold and pos[b] in ts[:3]:
-                death[b] = max(death[b], fold)
-    wrap = sorted(range(N), key=lambda b: (N - times[b][-1]) + death[b])
-    return set(wrap[:nres])
+        for t in ts[:3]:
+            death[perm[t]] = max(death[perm[t]], fold)
+    cand = sorted(((N - times[b][-1]) + death[b], b) for b in range(N) if times[b][-1] > death[b])
+    cur = clt256_sched.live_profile(rows, pos, LEAD).copy()
+    chosen = set()
+    for _, b in cand:
+        if len(chosen) >= nres:
+            break
+        done = times[b][-1]
+        add = np.zeros(N, dtype=np.int64)
+        add[done:] += 1
+        add[:pos[b]] += 1
+        fr = pos[b] - LEAD
+        if fr > done:
+            add[done:fr] -= 1          # the wait for its slot is already in the profile
+        if (cur + add).max() <= budget:
+            cur += add
+            chosen.add(b)
+    return chosen
+
+
+def slot_map(pos, resident):
+    """load time -> compact shared-memory slot, in load order, skipping resident planes"""
+    perm = [0] * N
+    for b, p in enumerate(pos):
+        perm[p] = b
+    m, k = {}, 0
+    for t in range(N):
+        if perm[t] not in resident:
+            m[t] = k
+            k += 1
+    return m
+
+
+RMW_FIRST = int(os.environ.get("CLT256V2_RMW_FIRST", "44"))   # first step with a histogram update
+RMW_EVERY = 6
+RMW_GAP = int(os.environ.get("CLT256V2_RMW_GAP", "5"))         # steps between its load and its store
+TAIL_STEPS = 40                                                # steps the previous clock's tail is spread over
 
 
 def rmw_hooks_v2():
-    """32 read-modify-writes of the private histogram (previous clock's samples, words z0..z7), one
-    every 8 steps: the load at step 8k+1, the store at step 8k+5."""
+    """32 read-modify-writes of the private histogram (words z0..z7 of the PREVIOUS clock, produced by
+    the tail code in the first TAIL_STEPS steps), one every RMW_EVERY steps."""
     hooks = {}
     k = 0
     for zi in range(8):
         for m in range(4):
             nm = "z%d_%d" % (zi, m)
-            hooks.setdefault(8 * k + 1, []).append("CLT256V2_RMW_LD(%s, z%d, %d)" % (nm, zi, m))
-            hooks.setdefault(8 * k + 5, []).append("CLT256V2_RMW_ST(%s)" % nm)
+            t0 = RMW_FIRST + RMW_EVERY * k
+            assert t0 + RMW_GAP < N and RMW_GAP < RMW_EVERY
+            hooks.setdefault(t0, []).append("CLT256V2_RMW_LD(%s, z%d, %d)" % (nm, zi, m))
+            hooks.setdefault(t0 + RMW_GAP, []).append("CLT256V2_RMW_ST(%s)" % nm)
             k += 1
     return hooks
 
 
-def body_hist_v2(rows, pos, resident):
+def tail_lines(shape):
+    """Finishes the popcount network of the previous clock from the carried planes k<w>_<i>
+    (shape[w] = [negated?, ...]) and un-slices the histogram indices into z0..z7."""
+    em = Emitter()
+    em.ntmp = 100000
+    heap = BitHeap(em)
+    for w, flags in enumerate(shape):
+        heap.heap[w] = [("k%d_%d" % (w, i), neg) for i, neg in enumerate(flags)]
+    planes = heap.finish()
+    for wgt in range(9):
+        em.emit("const uint32_t pc%d = %s;" % (wgt, planes[wgt]))
+    em.emit("const uint32_t inr = ~pc8 & ((~pc7 & pc6 & pc5) | (pc7 & ~pc6 & ~pc5));   // 96 <= popcount < 160")
+    em.emit("CLT256V2_AFTER_COUNT(pc0, pc1, pc2, pc3, pc4, pc5, pc6, pc7, pc8, inr)")
+    q = []
+    for b, src in enumerate(["pc0", "pc1", "pc2", "pc3", "pc4", "pc7"]):
+        nm = "q%d" % b
+        em.emit("const uint32_t %s = %s & inr;" % (nm, src))
+        q.append(nm)
+    gen_transpose(em, q, decl="const uint32_t ")
+    return em.lines, em.ops
+
+
+def carried_init(shape):
+    """Values of the carried planes before the first clock: a popcount of exactly 128 in every stream
+    (in range, private bin 32; the kernel takes those 32 counts back at the end)."""
+    need = 128
+    init = {}
+    for w in range(9, -1, -1):
+        for i, neg in enumerate(shape[w] if w < len(shape) else []):
+            one = need >= (1 << w)
+            if one:
+                need -= 1 << w
+            init["k%d_%d" % (w, i)] = 0xFFFFFFFF if (one != neg) else 0
+    assert need == 0, "carried shape cannot represent 128"
+    return init
+
+
+def body_hist_v2(rows, pos, resident, shape=None):
+    """shape None: dry run (returns the carried-plane shape); else the real body."""
     em = Emitter()
     perm = [0] * N
     for b, p in enumerate(pos):
@@ -83,6 +165,8 @@ def body_hist_v2(rows, pos, resident):
         for b in rows[r]:
             taps_at[pos[b]].append(r)
     hooks = rmw_hooks_v2()
+    tail, tail_ops = tail_lines(shape) if shape is not None else ([], {})
+    per_step = -(-len(tail) // TAIL_STEPS) if tail else 0
     heap = BitHeap(em)
     pending = {r: [] for r in range(N)}       # raw planes not yet folded
     acc = {}                                  # row -> partial sum expr
@@ -91,15 +175,17 @@ def body_hist_v2(rows, pos, resident):
     old_uses_left = {b: sum(1 for r in range(N) if b in rows[r]) for b in resident}
     assigned = set()
 
+    slot_of = slot_map(pos, resident)         # load time -> shared-memory slot (resident planes have none)
+
     def wexpr(t):
         b = perm[t]
         return ("r%d" % b) if b in resident else ("w%d" % t)
 
     def load(t):
         if t < N and perm[t] not in resident:
-            em.emit("const uint32_t w%d = st[%d * CLT256V2_B];" % (t, t))
-        for slot, ex in store_at.pop(t, []):
-            em.emit("st[%d * CLT256V2_B] = %s;" % (slot, ex))
+            em.emit("const uint32_t w%d = st[%d * CLT256V2_B];" % (t, slot_of[t]))
+        for tt, ex in store_at.pop(t, []):
+            em.emit("st[%d * CLT256V2_B] = %s;" % (slot_of[tt], ex))
 
     def finish(r, ex, t):
         if r in resident:
@@ -109,7 +195,7 @@ def body_hist_v2(rows, pos, resident):
             return
         slot = pos[r]
         if slot - LEAD <= t:
-            em.emit("st[%d * CLT256V2_B] = %s;" % (slot, ex))
+            em.emit("st[%d * CLT256V2_B] = %s;" % (slot_of[slot], ex))
         else:
             store_at.setdefault(slot, []).append((slot, ex))
 
@@ -117,6 +203,9 @@ def body_hist_v2(rows, pos, resident):
         load(t)
     for t in range(N):
         load(t + LEAD)
+        for ln in tail[:per_step]:
+            em.lines.append(ln)
+        del tail[:per_step]
         for ln in hooks.get(t, []):
             em.emit(ln)
         w = wexpr(t)
@@ -144,40 +233,49 @@ def body_hist_v2(rows, pos, resident):
                 em.ops["rec"] += 1
                 finish(r, nm, t)
     assert not store_at, store_at
+    assert not tail
     assert assigned == set(resident)
-    planes = heap.finish()
-    for wgt in range(9):
-        em.emit("const uint32_t pc%d = %s;" % (wgt, planes[wgt]))
-    em.emit("const uint32_t inr = ~pc8 & ((~pc7 & pc6 & pc5) | (pc7 & ~pc6 & ~pc5));   // 96 <= popcount < 160")
-    em.emit("CLT256V2_AFTER_COUNT(pc0, pc1, pc2, pc3, pc4, pc5, pc6, pc7, pc8, inr)")
-    q = []
-    for b, src in enumerate(["pc0", "pc1", "pc2", "pc3", "pc4", "pc7"]):
-        nm = "q%d" % b
-        em.emit("const uint32_t %s = %s & inr;" % (nm, src))
-        q.append(nm)
-    gen_transpose(em, q)
+    new_shape = [[neg for _, neg in heap.heap[w]] for w in range(10)]
+    if shape is None:
+        return new_shape
+    assert new_shape == shape
+    for w in range(10):
+        for i, (ex, _) in enumerate(heap.heap[w]):
+            em.emit("k%d_%d = %s;" % (w, i, ex))
+    for k in ("csa", "ha"):
+        em.ops[k] += tail_ops.get(k, 0)
     return em, perm
 
 
 def main():
     rows = recurrences.packed(N)
-    pos = run_annealer(rows)
+    pos = [int(v) for v in open(POS_FILE).read().split()] if POS_FILE else run_annealer(rows)
     peak = int(clt256_sched.live_profile(rows, pos, LEAD).max())
-    resident = pick_residents(rows, pos, NRES)
-    em, perm = body_hist_v2(rows, pos, resident)
+    resident = pick_residents(rows, pos, NRES, RES_BUDGET)
+    shape = body_hist_v2(rows, pos, resident)
+    em, perm = body_hist_v2(rows, pos, resident, shape)
+    init = carried_init(shape)
+    tail, _ = tail_lines(shape)
     out = os.path.join(ROOT, "basebandboard_b200", "csrc", "clt256_v2_gen.inc")
     with open(out, "w") as f:
         f.write("// GENERATED by tools/gen_clt256_v2.py -- do not edit.  One-pass LUTOPT(n256) clock + CLTGRNG popcount\n")
         f.write("// network + histogram indices on 32 bit-sliced streams (rng.py:38-40, :96-105; rng_recurrences.py:172-259).\n")
         f.write("// recurrence LOP3: %d, carry-save adders: %d, half adders: %d, modelled peak live values: %d, lead %d, resident %d\n"
                 % (em.ops["rec"], em.ops["csa"], em.ops["ha"], peak, LEAD, len(resident)))
-        f.write("#ifdef CLT256V2_SECTION_PERM\n// slot p (= load time p) holds state bit CLT256V2_PERM[p]\n")
-        f.write("static __constant__ uint8_t CLT256V2_PERM[256] = {%s};\n" % ", ".join(str(v) for v in perm))
+        sm = slot_map(pos, resident)
+        slot_bit = [perm[t] for t in range(N) if t in sm]
+        f.write("#ifdef CLT256V2_SECTION_PERM\n// shared-memory slot s holds state bit CLT256V2_SLOT_BIT[s]; the other planes stay in registers\n")
+        f.write("#define CLT256V2_NSLOTS %d\n" % len(slot_bit))
+        f.write("static __constant__ uint8_t CLT256V2_SLOT_BIT[%d] = {%s};\n" % (len(slot_bit), ", ".join(str(v) for v in slot_bit)))
         f.write("#endif\n#ifdef CLT256V2_SECTION_RESIDENT_DECL\n")
         for b in sorted(resident):
-            f.write("    uint32_t r%d = st[%d * CLT256V2_B];\n" % (b, pos[b]))
+            f.write("    uint32_t r%d = planes[(size_t)%d * T + t];\n" % (b, b))
+        for nm, v in init.items():
+            f.write("    uint32_t %s = 0x%08xu;\n" % (nm, v))
         f.write("#endif\n#ifdef CLT256V2_SECTION_BODY\n")
         f.write("\n".join(em.lines))
+        f.write("\n#endif\n#ifdef CLT256V2_SECTION_TAIL\n// the last clock's popcount planes -> z0..z7\n")
+        f.write("\n".join(tail))
         f.write("\n#endif\n")
     print("wrote", out, "ops", em.ops, "peak live", peak, "resident", len(resident), file=sys.stderr)
 
