@@ -30,30 +30,45 @@ seed_kernel(const uint32_t *__restrict__ J,   // [nbits][n][NW32] column-major j
     const uint32_t lane = threadIdx.x & 31;
     if (gw >= T) return;
     const uint32_t s = gw * 32 + lane;   // stream index
-    uint32_t x[NW32];
+    // The warp works on ONE state at a time, replicated in every lane: a jump operator is applied
+    // cooperatively (lane l folds columns l, l+32, ... -- coalesced reads of the column-major operator --
+    // then an XOR butterfly leaves the product in all lanes).  First the bits of the stream index the
+    // whole warp shares (b >= 5), then 31 successive applications of J[0] = A^L; lane l keeps the state
+    // after l of them: A^(s*L) x with s = 32*gw + l.
+    uint32_t y[NW32], x[NW32];
 #pragma unroll
-    for (int w = 0; w < NW32; w++) x[w] = xs.w[w];
-    for (uint32_t b = 0; b < nbits; b++) {
-        const bool mine = (s >> b) & 1;
-        if (!__any_sync(0xffffffffu, mine)) continue;   // warp-uniform for b >= 5
-        const uint32_t *Jb = J + (size_t)b * n * NW32;
+    for (int w = 0; w < NW32; w++) y[w] = xs.w[w];
+    auto apply = [&](const uint32_t *Jb) {
         uint32_t acc[NW32];
 #pragma unroll
         for (int w = 0; w < NW32; w++) acc[w] = 0;
 #pragma unroll
-        for (int xw = 0; xw < NW32; xw++) {
-            const uint32_t word = x[xw];
-            const uint32_t cend = min(32u, n - (uint32_t)xw * 32u);
-            for (uint32_t k = 0; k < cend; k++) {
-                const uint32_t m = 0u - ((word >> k) & 1u);
-                const uint32_t *col = Jb + (size_t)(xw * 32 + k) * NW32;
+        for (int k = 0; k < NW32; k++) {
+            const uint32_t col = (uint32_t)k * 32u + lane;
+            if (col < n && ((y[k] >> lane) & 1u)) {
+                const uint32_t *cp = Jb + (size_t)col * NW32;
 #pragma unroll
-                for (int w = 0; w < NW32; w++) acc[w] ^= __ldg(col + w) & m;
+                for (int w = 0; w < NW32; w++) acc[w] ^= __ldg(cp + w);
             }
         }
-        if (mine) {
 #pragma unroll
-            for (int w = 0; w < NW32; w++) x[w] = acc[w];
+        for (int off = 16; off >= 1; off >>= 1)
+#pragma unroll
+            for (int w = 0; w < NW32; w++) acc[w] ^= __shfl_xor_sync(0xffffffffu, acc[w], off);
+#pragma unroll
+        for (int w = 0; w < NW32; w++) y[w] = acc[w];
+    };
+    for (uint32_t b = 5; b < nbits; b++)
+        if ((gw >> (b - 5)) & 1u) apply(J + (size_t)b * n * NW32);
+#pragma unroll
+    for (int w = 0; w < NW32; w++) x[w] = y[w];
+    if (nbits > 0) {
+        for (uint32_t l = 1; l < 32; l++) {
+            apply(J);
+            if (lane == l) {
+#pragma unroll
+                for (int w = 0; w < NW32; w++) x[w] = y[w];
+            }
         }
     }
     // ballot transpose: word i of thread gw = bit i of every lane's state
@@ -236,7 +251,7 @@ static int launch_seed(bbb_ctx *c, const uint32_t *dJ, const SeedStart &xs, uint
 
 // clt_spec.cu
 int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only);
-int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c);
+int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c, int kind);
 int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model, const uint32_t *planes,
                         unsigned long long *hist);
 int bbb_clt_spec_stream_ok(const bbb_ctx *c, int kind);
@@ -335,7 +350,7 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
     // 2 raw words, 3 int16 scaled samples, -1 none
     int kind = -1;
     if (d_hist && !d_out8 && !d_out16 && !d_out_words32) kind = 0;
-    else if (d_out8 && !d_hist && !d_out16 && !d_out_words32 && ((uintptr_t)d_out8 & 7) == 0) kind = 1;
+    else if (d_out8 && !d_hist && !d_out16 && !d_out_words32 && ((uintptr_t)d_out8 & 31) == 0) kind = 1;
     else if (d_out_words32 && !d_hist && !d_out8 && !d_out16 && ((uintptr_t)d_out_words32 & 15) == 0) kind = 2;
     else if (d_out16 && !d_hist && !d_out8 && !d_out_words32 && ((uintptr_t)d_out16 & 15) == 0) kind = 3;
     uint64_t spb = 0;
@@ -348,17 +363,18 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
         const uint64_t rem = count - done;
 
         // ---- specialised kernel: `blocks` CTAs x spb streams x L clocks, one wave ----
-        if (spb && ((kind != 1 && kind != 3) || (done & 7) == 0)) {
+        if (spb && ((kind != 1 && kind != 3) || (done & 31) == 0)) {
             const uint64_t max_blocks = c->tune_spec_max_blocks ? c->tune_spec_max_blocks
-                                        : (uint64_t)c->sm_count * (kind == 0 ? bbb_clt_spec_blocks_per_sm(c) : 1);
+                                        : (uint64_t)c->sm_count * bbb_clt_spec_blocks_per_sm(c, kind);
             // fewest clocks per stream worth a launch (the stream kernels amortise their seeding sooner)
-            const uint64_t min_steps = kind > 0 ? (c->tune_spec_min_steps / 4 > 8 ? c->tune_spec_min_steps / 4 : 8)
-                                                : c->tune_spec_min_steps;
+            const uint64_t min_steps = kind == 2   ? (c->tune_spec_min_steps / 4 > 8 ? c->tune_spec_min_steps / 4 : 8)
+                                       : kind > 0 ? (c->tune_spec_min_steps / 4 > 32 ? c->tune_spec_min_steps / 4 : 32)
+                                                  : c->tune_spec_min_steps;
             uint64_t blocks = rem / (spb * min_steps);
             if (blocks > max_blocks) blocks = max_blocks;
             uint64_t L = blocks ? rem / (blocks * spb) : 0;
             if (L > (1ull << 26)) L = 1ull << 26;          // private u32 bins: 32 * L < 2^32
-            if (kind == 1 || kind == 3) L &= ~7ull;         // 8 clocks per store
+            if (kind == 1 || kind == 3) L &= ~31ull;        // 32 clocks per flush (one full sector per stream)
             if (blocks >= 1 && L >= 8) {
                 const uint64_t S = blocks * spb;
                 const uint32_t T = (uint32_t)(S / 32);

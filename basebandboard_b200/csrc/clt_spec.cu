@@ -204,7 +204,10 @@ clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
 }
 
 // CTAs of the fused kernel one SM holds at a time
-int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c) { return c->tune_spec_variant == 1 ? 1 : CLT256V2_CTAS_PER_SM; }
+int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c, int kind)
+{
+    return c->tune_spec_variant == 1 || kind == 2 ? 1 : CLT256V2_CTAS_PER_SM;
+}
 
 // Streams one CTA carries, and whether the loaded recurrence has a specialised kernel.
 int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only)
@@ -339,6 +342,92 @@ clt256_s8_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, in
     }
 }
 
+// One-pass variant of the sample-stream kernel (tools/gen_clt256_v2.py, kind "s8"): same clock as
+// clt256_hist2_kernel; the tail of clock it-1 (popcount -> int8 -> 8x8 un-slice) runs inside iteration it.
+// A stream's bytes are 1 per clock, and 1.2 M streams are open at a time: 8-byte pieces written
+// straight to their final place (the two-pass kernel) leave partial sectors that fall out of L2 and
+// cost a DRAM read-modify-write each (measured: 215 GB/s however fast the ALU side is).  Here the 8
+// un-sliced words of a clock go to a global slab [clock % 32][word][thread] with coalesced 128-byte
+// stores (it stays in L2: 1 KB per thread), and every 32 clocks a thread reads its slab column back,
+// finishes the byte transpose and writes one full 32-byte sector per stream (64 B for int16).
+#define CLT256V2_S8_K 32
+#define CLT256V2_S8_STAGE(z0, z1, z2, z3, z4, z5, z6, z7)                                  \
+    {                                                                                      \
+        uint32_t *const sp = slab + (size_t)(((it - 1u) & (CLT256V2_S8_K - 1u)) * 8u) * T; \
+        __stcg(sp, z0);                                                                    \
+        __stcg(sp + (size_t)T, z1);                                                        \
+        __stcg(sp + (size_t)2 * T, z2);                                                    \
+        __stcg(sp + (size_t)3 * T, z3);                                                    \
+        __stcg(sp + (size_t)4 * T, z4);                                                    \
+        __stcg(sp + (size_t)5 * T, z5);                                                    \
+        __stcg(sp + (size_t)6 * T, z6);                                                    \
+        __stcg(sp + (size_t)7 * T, z7);                                                    \
+    }
+
+// clocks c0 .. c0+31 of this thread's 32 streams: slab -> final place
+__device__ __forceinline__ void clt256v2_s8_flush(const uint32_t *slab, uint32_t T, int8_t *outp, uint32_t c0, uint32_t L,
+                                                  bool OUT16, int32_t noise_var)
+{
+    int8_t *const o8 = outp + (size_t)c0 * (OUT16 ? 2u : 1u);
+#pragma unroll 1
+    for (int s = 0; s < 8; s++) {
+        uint32_t W[CLT256V2_S8_K], o[CLT256V2_S8_K / 4][4];
+#pragma unroll
+        for (int tau = 0; tau < CLT256V2_S8_K; tau++) W[tau] = __ldcg(slab + (size_t)(tau * 8 + s) * T);
+#pragma unroll
+        for (int g = 0; g < CLT256V2_S8_K / 4; g++) bytes4x4(W[4 * g], W[4 * g + 1], W[4 * g + 2], W[4 * g + 3], o[g]);
+#pragma unroll
+        for (int m = 0; m < 4; m++) {          // byte lane m of word s = stream 8m+s
+            if (OUT16) {
+                uint4 *const d = (uint4 *)(o8 + (size_t)(8 * m + s) * L * 2u);
+#pragma unroll
+                for (int g = 0; g < CLT256V2_S8_K / 4; g += 2) {
+                    const uint2 a = scale4(o[g][m], noise_var), b = scale4(o[g + 1][m], noise_var);
+                    __stcs(d + g / 2, make_uint4(a.x, a.y, b.x, b.y));
+                }
+            } else {
+                uint4 *const d = (uint4 *)(o8 + (size_t)(8 * m + s) * L);
+#pragma unroll
+                for (int g = 0; g < CLT256V2_S8_K / 4; g += 4)
+                    __stcs(d + g / 4, make_uint4(o[g][m], o[g + 1][m], o[g + 2][m], o[g + 3][m]));
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(CLT256V2_B, CLT256V2_CTAS_PER_SM)
+clt256_s8v2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, int8_t *__restrict__ out,
+                   int32_t noise_var, uint32_t *__restrict__ slab_base)
+{
+    const bool OUT16 = noise_var >= 0;
+    extern __shared__ uint4 smem4[];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+    uint32_t *const st = (uint32_t *)smem4 + tid;
+    for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+    uint32_t *const slab = slab_base + t;
+    int8_t *const outp = out + (size_t)t * 32u * L * (OUT16 ? 2u : 1u);   // stream j: sample offset j*L
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_S8_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_S8_BODY
+        if ((it & (CLT256V2_S8_K - 1u)) == 0u && it != 0u)
+            clt256v2_s8_flush(slab, T, outp, it - CLT256V2_S8_K, L, OUT16, noise_var);
+    }
+    {
+        const uint32_t it = L;       // the last clock's tail (L is a multiple of 32: it lands in slab row 31)
+#define CLT256V2_SECTION_S8_TAIL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_S8_TAIL
+        clt256v2_s8_flush(slab, T, outp, L - CLT256V2_S8_K, L, OUT16, noise_var);
+    }
+}
+
 // raw URNG words (LUTOPT.x after every clock, rng.py:27): 32 x 32 bit transposes of the new planes,
 // four 32-bit words of a stream leave as one 128-bit store (a stream's clock = one 32-byte sector)
 #define CLT256W_SECTION_PERM
@@ -403,7 +492,17 @@ int bbb_clt_spec_stream_ok(const bbb_ctx *c, int kind)
 int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L, const uint32_t *planes, void *out,
                                uint32_t noise_var)
 {
-    if (kind == 1) {
+    if ((kind == 1 || kind == 3) && c->tune_spec_variant != 1) {
+        static_assert(CLT256V2_CTAS_PER_SM * (CLT256V2_STATE_BYTES + 1024) <= 228 * 1024, "shared memory budget");
+        const uint32_t T = blocks * CLT256V2_B;
+        uint32_t *slab = (uint32_t *)c->scratch(11, (size_t)CLT256V2_S8_K * 8 * T * 4);
+        if (!slab) return BBB_ECUDA;
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_s8v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         CLT256V2_STATE_BYTES));
+        clt256_s8v2_kernel<<<blocks, CLT256V2_B, CLT256V2_STATE_BYTES, c->stream>>>(
+            planes, T, L, (int8_t *)out, kind == 1 ? -1 : (int32_t)noise_var, slab);
+        c->last_kernel = kind == 1 ? "clt256_s8v2" : "clt256_s16v2";
+    } else if (kind == 1) {
         static_assert(CLT256S8_SMEM <= 227 * 1024, "shared memory budget");
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_s8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256S8_SMEM));
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out, -1);

@@ -198,19 +198,25 @@ def test_spec256_equals_generic_large(ctx):
 
 
 # ---- the specialised n256 stream kernels (clt256_s8, clt256_words) ---------------------------------
-@pytest.mark.parametrize("blocks,min_steps,count,first", [(1, 8, 4096 * 24 + 77, 0), (2, 16, 2 * 4096 * 40 + 13, (1 << 33) + 5)])
-def test_spec256_int8_stream_matches_oracle(ctx, orc, blocks, min_steps, count, first):
-    """Straight-line kernel with on-chip bit->byte transpose and 64-bit stores + generic tail == oracle."""
+@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("blocks,min_steps,count,first", [(1, 8, 4096 * 24 + 77, 0), (2, 16, 2 * 4096 * 40 + 13, (1 << 33) + 5),
+                                                         (1, 8, 4096 * 75 + 31, 64), (3, 8, 3 * 4096 * 130 + 5, (1 << 40) + 32)])
+def test_spec256_int8_stream_matches_oracle(ctx, orc, blocks, min_steps, count, first, variant):
+    """Straight-line kernels (two-pass clt256_s8, one-pass clt256_s8v2) with on-chip bit->byte transpose
+    and 64-bit stores + generic tail == oracle."""
     ctx.lutopt_load_shipped(256)
+    ctx.set_tuning("clt_spec_variant", variant)
     ctx.set_tuning("clt_spec_min_steps", min_steps)
     ctx.set_tuning("clt_spec_max_blocks", blocks)
     try:
         got = ctx.clt_stream(1, first, count, model=0)
+        assert ctx.last_launches >= 2          # a specialised launch happened (then the generic tail)
         ref = orc.clt_run(recurrences.packed(256), 1, first, count, model=0, want=("out8",))
         assert np.array_equal(got, ref["out8"])
     finally:
         ctx.set_tuning("clt_spec_min_steps", 512)
         ctx.set_tuning("clt_spec_max_blocks", 0)
+        ctx.set_tuning("clt_spec_variant", 2)
 
 
 @pytest.mark.parametrize("blocks,min_steps,count,first", [(1, 8, 4096 * 9 + 5, 0), (2, 8, 2 * 4096 * 11 + 3, (1 << 35) + 1)])
@@ -237,7 +243,16 @@ def test_spec256_streams_equal_generic_large(ctx):
     b = torch.empty(count, dtype=torch.int8, device="cuda")
     ctx.clt_stream_dev(1, 99, count, 0, 1, a.data_ptr(), 1)
     ctx.sync()
-    assert ctx.last_kernel in ("clt256_s8", "generic") and ctx.last_launches >= 2
+    assert ctx.last_kernel in ("clt256_s8v2", "generic") and ctx.last_launches >= 2
+    ctx.set_tuning("clt_spec_variant", 1)
+    try:
+        ctx.clt_stream_dev(1, 99, count, 0, 1, b.data_ptr(), 1)
+        ctx.sync()
+        assert ctx.last_kernel in ("clt256_s8", "generic")
+    finally:
+        ctx.set_tuning("clt_spec_variant", 2)
+    assert bool(torch.equal(a, b))
+    b.zero_()
     ctx.set_tuning("clt_no_spec", 1)
     try:
         ctx.clt_stream_dev(1, 99, count, 0, 1, b.data_ptr(), 1)
@@ -265,18 +280,21 @@ def test_spec256_streams_equal_generic_large(ctx):
     assert bool(torch.equal(wa, wb))
 
 
+@pytest.mark.parametrize("variant", [1, 2])
 @pytest.mark.parametrize("noise_var", [0, 1, 8, 15])
-def test_spec256_int16_noise_stream_matches_oracle(ctx, orc, noise_var):
-    """tx.py:75-76: noise = g * noise_var as int16, straight-line kernel + generic tail == oracle."""
+def test_spec256_int16_noise_stream_matches_oracle(ctx, orc, noise_var, variant):
+    """tx.py:75-76: noise = g * noise_var as int16, straight-line kernels + generic tail == oracle."""
     ctx.lutopt_load_shipped(256)
+    ctx.set_tuning("clt_spec_variant", variant)
     ctx.set_tuning("clt_spec_min_steps", 16)
     ctx.set_tuning("clt_spec_max_blocks", 2)
     try:
-        count, first = 2 * 4096 * 24 + 21, 1234567
+        count, first = 2 * 4096 * 72 + 21, 1234567
         got = ctx.clt_stream(1, first, count, model=0, noise_var=noise_var)
-        assert ctx.last_kernel in ("clt256_s16", "generic")
+        assert ctx.last_kernel in ("clt256_s16" if variant == 1 else "clt256_s16v2", "generic")
         ref = orc.clt_run(recurrences.packed(256), 1, first, count, model=0, noise_var=noise_var, want=("out16",))
         assert np.array_equal(got, ref["out16"])
     finally:
         ctx.set_tuning("clt_spec_min_steps", 512)
         ctx.set_tuning("clt_spec_max_blocks", 0)
+        ctx.set_tuning("clt_spec_variant", 2)

@@ -27,9 +27,11 @@ N = 256
 LEAD = int(os.environ.get("CLT256V2_LEAD", "6"))          # loads are issued this many steps ahead
 ITERS = int(os.environ.get("CLT256V2_ITERS", "12000000"))
 SEED = int(os.environ.get("CLT256V2_SEED", "1"))
-NRES = int(os.environ.get("CLT256V2_RESIDENT", "0"))      # most planes kept in registers across clocks
-RES_BUDGET = int(os.environ.get("CLT256V2_RES_BUDGET", "132"))   # modelled live values allowed with them
-POS_FILE = os.environ.get("CLT256V2_POS")                 # reuse a load order (one integer per line)
+NRES = int(os.environ.get("CLT256V2_RESIDENT", "104"))    # most planes kept in registers across clocks
+RES_BUDGET = int(os.environ.get("CLT256V2_RES_BUDGET", "200"))   # modelled live values allowed with them
+# the committed load order (annealer output, 3M iterations, seed 1, lead 6); CLT256V2_REANNEAL=1 recomputes it
+POS_FILE = None if os.environ.get("CLT256V2_REANNEAL") else \
+    os.environ.get("CLT256V2_POS", os.path.join(ROOT, "tools", "clt256_v2_order.txt"))
 
 
 def run_annealer(rows):
@@ -117,9 +119,10 @@ def rmw_hooks_v2():
     return hooks
 
 
-def tail_lines(shape):
+def tail_lines(shape, kind="hist"):
     """Finishes the popcount network of the previous clock from the carried planes k<w>_<i>
-    (shape[w] = [negated?, ...]) and un-slices the histogram indices into z0..z7."""
+    (shape[w] = [negated?, ...]) and un-slices into z0..z7: the histogram indices (kind "hist"), or the
+    int8 samples g = popcount - 128 in two's complement, gateware width rng.py:78 (kind "s8")."""
     em = Emitter()
     em.ntmp = 100000
     heap = BitHeap(em)
@@ -128,6 +131,11 @@ def tail_lines(shape):
     planes = heap.finish()
     for wgt in range(9):
         em.emit("const uint32_t pc%d = %s;" % (wgt, planes[wgt]))
+    if kind == "s8":
+        em.emit("const uint32_t pc7n = ~pc7;")
+        gen_transpose(em, ["pc0", "pc1", "pc2", "pc3", "pc4", "pc5", "pc6", "pc7n"], decl="const uint32_t ")
+        em.emit("CLT256V2_S8_STAGE(z0, z1, z2, z3, z4, z5, z6, z7)")
+        return em.lines, em.ops
     em.emit("const uint32_t inr = ~pc8 & ((~pc7 & pc6 & pc5) | (pc7 & ~pc6 & ~pc5));   // 96 <= popcount < 160")
     em.emit("CLT256V2_AFTER_COUNT(pc0, pc1, pc2, pc3, pc4, pc5, pc6, pc7, pc8, inr)")
     q = []
@@ -154,7 +162,7 @@ def carried_init(shape):
     return init
 
 
-def body_hist_v2(rows, pos, resident, shape=None):
+def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
     """shape None: dry run (returns the carried-plane shape); else the real body."""
     em = Emitter()
     perm = [0] * N
@@ -164,8 +172,8 @@ def body_hist_v2(rows, pos, resident, shape=None):
     for r in range(N):
         for b in rows[r]:
             taps_at[pos[b]].append(r)
-    hooks = rmw_hooks_v2()
-    tail, tail_ops = tail_lines(shape) if shape is not None else ([], {})
+    hooks = rmw_hooks_v2() if kind == "hist" else {}
+    tail, tail_ops = tail_lines(shape, kind) if shape is not None else ([], {})
     per_step = -(-len(tail) // TAIL_STEPS) if tail else 0
     heap = BitHeap(em)
     pending = {r: [] for r in range(N)}       # raw planes not yet folded
@@ -256,6 +264,8 @@ def main():
     em, perm = body_hist_v2(rows, pos, resident, shape)
     init = carried_init(shape)
     tail, _ = tail_lines(shape)
+    em8, _ = body_hist_v2(rows, pos, resident, shape, "s8")
+    tail8, _ = tail_lines(shape, "s8")
     out = os.path.join(ROOT, "basebandboard_b200", "csrc", "clt256_v2_gen.inc")
     with open(out, "w") as f:
         f.write("// GENERATED by tools/gen_clt256_v2.py -- do not edit.  One-pass LUTOPT(n256) clock + CLTGRNG popcount\n")
@@ -276,6 +286,10 @@ def main():
         f.write("\n".join(em.lines))
         f.write("\n#endif\n#ifdef CLT256V2_SECTION_TAIL\n// the last clock's popcount planes -> z0..z7\n")
         f.write("\n".join(tail))
+        f.write("\n#endif\n#ifdef CLT256V2_SECTION_S8_BODY\n// same clock, int8 samples instead of histogram indices\n")
+        f.write("\n".join(em8.lines))
+        f.write("\n#endif\n#ifdef CLT256V2_SECTION_S8_TAIL\n")
+        f.write("\n".join(tail8))
         f.write("\n#endif\n")
     print("wrote", out, "ops", em.ops, "peak live", peak, "resident", len(resident), file=sys.stderr)
 
