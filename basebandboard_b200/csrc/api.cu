@@ -96,13 +96,18 @@ void *bbb_ctx::scratch(int slot, size_t bytes)
 
 void bbb_ctx::begin_call()
 {
+    if (nest) return;      // inside a composite call: one timing region, counters keep adding up
     last_ms = 0.0;
     last_launches = 0;
     h2d_bytes = d2h_bytes = 0;
     cudaEventRecord(ev0, stream);
 }
 
-void bbb_ctx::end_call() { cudaEventRecord(ev1, stream); }
+void bbb_ctx::end_call()
+{
+    if (nest) return;
+    cudaEventRecord(ev1, stream);
+}
 
 const HostMat &bbb_ctx::pow2(uint32_t i)
 {
@@ -202,6 +207,7 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
     else if (!strcmp(key, "clt_spec_variant")) c->tune_spec_variant = value == 1 ? 1 : 2;
     else if (!strcmp(key, "clt_spec_min_steps")) c->tune_spec_min_steps = value < 1 ? 1u : (uint32_t)value;
     else if (!strcmp(key, "clt_spec_max_blocks")) c->tune_spec_max_blocks = value < 0 ? 0u : (uint32_t)value;
+    else if (!strcmp(key, "slicer_chunk_bits")) c->tune_slicer_chunk_bits = value < 64 ? 0ull : ((uint64_t)value & ~63ull);
     else if (!strcmp(key, "prbs_chunk_words")) c->tune_prbs_chunk_words = value < 0 ? 0u : (uint32_t)value;
     else if (!strcmp(key, "hunt_smem_taps")) c->tune_hunt_smem_taps = (int)value;
     else if (!strcmp(key, "hunt_slow_check")) c->tune_hunt_slow_check = value != 0;

@@ -53,6 +53,8 @@ struct bbb_ctx {
     int tune_spec_variant = 2;          // fused n256 kernel: 1 two-pass (clt256_gen.inc), 2 one-pass (clt256_v2_gen.inc)
     uint32_t tune_spec_min_steps = 512; // fewest clocks per stream worth a specialised launch
     uint32_t tune_spec_max_blocks = 0;  // 0: one CTA per SM
+    uint64_t tune_slicer_chunk_bits = 0; // 0: 2^27 PRBS bits per pass of the slicer-loop composite
+    int nest = 0;                       // > 0 inside a composite ABI call (begin_call/end_call are the outer call's)
     uint32_t tune_prbs_chunk_words = 0; // 0: automatic detector chunk length (64-bit words)
     uint32_t tune_prbs_stream_reps = 0; // 0: automatic stream-kernel repetitions per warp
     int tune_hunt_smem_taps = 0;        // 1: never use the taps-in-registers front kernel

@@ -235,6 +235,7 @@ struct DetectParams {
     uint4 *end_prev, *end_cur; // [nchunks] double-buffered end states
     unsigned long long *ctr;   // [5][nchunks]
     uint32_t *changed;
+    const uint64_t *err_words; // caller-supplied channel errors (word j = bits [64j, 64j+64) after first_bit), or null
 };
 
 // DESIGN.md "channel": Bernoulli(2^-m) error word for absolute bits [64W, 64W+64): the AND of m
@@ -313,7 +314,7 @@ prbs_detect_kernel(DetectParams p)
     if (!have_start) {
         // locked, nothing pending: bit_in = received b[p-1], prbs = s_{p-1}, err_sr = the error bits
         // of the K cycles before, reload_ctr = 0
-        const uint64_t eprev = err_bits_at(p.seed, p.first_bit + bit0 - 64, p.err_m);
+        const uint64_t eprev = p.err_words ? p.err_words[w0 - 1] : err_bits_at(p.seed, p.first_bit + bit0 - 64, p.err_m);
         start.x = (uint32_t)((wprev ^ eprev) >> 63);
         start.y = s_pm1;
         start.z = (uint32_t)__brevll(eprev << 1) & MASK;
@@ -333,7 +334,7 @@ prbs_detect_kernel(DetectParams p)
         tpos = tpos + 1 == K ? 0 : tpos + 1;
 
         const uint32_t nb = bits_left - (j << 6) >= 64 ? 64u : (uint32_t)(bits_left - (j << 6));
-        uint64_t e = err_bits_at(p.seed, p.first_bit + bit0 + (j << 6), p.err_m);
+        uint64_t e = p.err_words ? p.err_words[w0 + j] : err_bits_at(p.seed, p.first_bit + bit0 + (j << 6), p.err_m);
         if (nb < 64) e &= (1ull << nb) - 1;
         n_inj += __popcll(e);
         const uint64_t r = w ^ e;                                     // received bits
@@ -550,8 +551,12 @@ int bbb_prbs_spec_state(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint32_t err
     return BBB_OK;
 }
 
-int bbb_prbs_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, uint32_t err_m, uint64_t seed,
-                    bbb_det_state *det, bbb_det_counters *ctr)
+}  // extern "C"
+
+// the detector over a bit range; the channel is the keyed Bernoulli source (err_words null) or the
+// caller's error words on the device
+static int detect_impl(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, uint32_t err_m, uint64_t seed,
+                       const uint64_t *err_words, bbb_det_state *det, bbb_det_counters *ctr)
 {
     int rc = check_prbs_args(c, k, 0);
     if (rc) return rc;
@@ -572,6 +577,7 @@ int bbb_prbs_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, 
     p.s_m1 = host_prbs_unstep(k, tap, host_jump(*ht, k, 1u, first_bit));
     p.err_m = err_m;
     p.seed = seed;
+    p.err_words = err_words;
     p.first_bit = first_bit;
     p.nbits = nbits;
     const uint64_t nwords = (nbits + 63) / 64;
@@ -641,6 +647,92 @@ int bbb_prbs_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, 
         det->err_sr = (uint32_t)out[7];
         det->reload_ctr = (uint32_t)out[8];
     }
+    return BBB_OK;
+}
+
+// AWGN slicer channel (tx.py:75-81, rx.py:28): the transmitted sample of bit b is +A or -A plus
+// noise = g * noise_var, registered as a 12-bit signed word (wraps like the gateware's Signal((12, True)));
+// the receiver slices it at 0 (sliced = ~sample[-1]) and takes sample `delay` of the spb samples of a bit.
+// One thread per 64 bits: err word = sliced bits XOR transmitted bits.
+__global__ void __launch_bounds__(256)
+slicer_err_kernel(const int8_t *__restrict__ g, const uint64_t *__restrict__ tx, uint64_t nwords, uint32_t spb,
+                  uint32_t delay, int32_t amp, int32_t noise_var, uint64_t *__restrict__ err)
+{
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nwords) return;
+    const uint64_t w = tx[j];
+    const int8_t *gp = g + (j * 64) * spb + delay;
+    uint64_t rx = 0;
+#pragma unroll 4
+    for (uint32_t i = 0; i < 64; i++) {
+        const int32_t noise = (int32_t)gp[(size_t)i * spb] * noise_var;
+        const int32_t x = (((w >> i) & 1ull) ? amp : -amp) + noise;
+        const int32_t x12 = ((x + 2048) & 4095) - 2048;
+        rx |= (uint64_t)(x12 >= 0) << i;
+    }
+    err[j] = rx ^ w;
+}
+
+extern "C" {
+
+int bbb_prbs_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, uint32_t err_m, uint64_t seed,
+                    bbb_det_state *det, bbb_det_counters *ctr)
+{
+    return detect_impl(c, k, first_bit, nbits, err_m, seed, nullptr, det, ctr);
+}
+
+int bbb_prbs_detect_errs_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, const uint64_t *err_words_dev,
+                             bbb_det_state *det, bbb_det_counters *ctr)
+{
+    if (!c) return BBB_EINVAL;
+    if (!err_words_dev) return c->fail(BBB_EINVAL, "err_words_dev is null");
+    return detect_impl(c, k, first_bit, nbits, 0, 0, err_words_dev, det, ctr);
+}
+
+int bbb_prbs_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, const uint64_t *x0,
+                           uint32_t amplitude, uint32_t noise_var, uint32_t spb, uint32_t delay, bbb_det_state *det,
+                           bbb_det_counters *ctr)
+{
+    int rc = check_prbs_args(c, k, 0);
+    if (rc) return rc;
+    if (!ctr || !x0) return c->fail(BBB_EINVAL, "null argument");
+    if (nbits & 63) return c->fail(BBB_EINVAL, "nbits must be a multiple of 64");
+    if (amplitude > 2047 || noise_var > 15) return c->fail(BBB_EINVAL, "amplitude 0..2047, noise_var 0..15 (tx.py:46-49)");
+    if (!spb || (spb & (spb - 1)) || spb > 16 || delay >= spb)
+        return c->fail(BBB_EINVAL, "spb must be a power of two <= 16 and delay < spb (rx.py:18-19)");
+    if (c->n == 0 || c->n > 256) return c->fail(BBB_ESTATE, "load a recurrence with n <= 256 first");
+    if ((first_bit + nbits) >> 58) return c->fail(BBB_EINVAL, "bit range too large");
+    bbb_det_state d0;
+    if (det) d0 = *det;
+    else { d0.bit_in = 0; d0.prbs = 1; d0.err_sr = (uint32_t)((1ull << k) - 1); d0.reload_ctr = 0; }
+    c->begin_call();
+    struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
+    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 27);
+    uint32_t rounds = 0;
+    for (uint64_t off = 0; off < nbits; off += CH) {
+        const uint64_t nb = nbits - off < CH ? nbits - off : CH, nw = nb / 64;
+        int8_t *d_g = (int8_t *)c->scratch(9, (size_t)nb * spb);
+        uint64_t *d_tx = (uint64_t *)c->scratch(10, (size_t)nw * 16);
+        if (!d_g || !d_tx) return BBB_ECUDA;
+        uint64_t *d_err = d_tx + nw;
+        rc = bbb_prbs_stream_dev(c, k, 1u, first_bit + off, nb, d_tx);
+        if (rc) return rc;
+        rc = bbb_clt_stream_dev(c, x0, (first_bit + off) * spb, nb * spb, BBB_MODEL_GATEWARE, 1u, d_g, nullptr);
+        if (rc) return rc;
+        slicer_err_kernel<<<(uint32_t)((nw + 255) / 256), 256, 0, c->stream>>>(d_g, d_tx, nw, spb, delay, (int32_t)amplitude,
+                                                                                (int32_t)noise_var, d_err);
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        rc = detect_impl(c, k, first_bit + off, nb, 0, 0, d_err, &d0, ctr);
+        if (rc) return rc;
+        rounds += c->last_rounds;
+    }
+    c->last_rounds = rounds;
+    c->last_kernel = "prbs_slicer_detect";
+    if (det) *det = d0;
+    c->nest--;          // close the outer timing region (the guard's decrement is balanced below)
+    c->end_call();
+    c->nest++;
     return BBB_OK;
 }
 

@@ -78,6 +78,10 @@ SIGNATURES = {
                                       C.c_void_p]),
     "bbb_prbs_detect": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32,
                                   C.c_uint64, _P(DetState), _P(DetCounters)]),
+    "bbb_prbs_detect_errs_dev": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, C.c_void_p,
+                                           _P(DetState), _P(DetCounters)]),
+    "bbb_prbs_slicer_detect": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, _u64p, C.c_uint32, C.c_uint32,
+                                         C.c_uint32, C.c_uint32, _P(DetState), _P(DetCounters)]),
     "bbb_prbs_spec_state": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, _P(DetState)]),
     "bbb_last_rounds": (C.c_uint32, [_ctx]),
     "bbb_rnghunt_eval": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, _u64p, _u8p, _u64p]),
@@ -288,6 +292,23 @@ class Context:
         self._check(self._L.bbb_prbs_detect(self._h, k, first_bit, nbits, m, seed,
                                             C.byref(det) if det is not None else None,
                                             C.byref(ctr)))
+        return ctr.as_dict()
+
+    def prbs_detect_errs_dev(self, k, nbits, err_words_dev_ptr, first_bit=0, det=None):
+        """PRBSErrorDetector (prbs.py:43-99) behind a caller-supplied error pattern (device u64 words)."""
+        ctr = DetCounters()
+        self._check(self._L.bbb_prbs_detect_errs_dev(self._h, k, first_bit, nbits, C.c_void_p(err_words_dev_ptr),
+                                                     C.byref(det) if det is not None else None, C.byref(ctr)))
+        return ctr.as_dict()
+
+    def prbs_slicer_detect(self, k, nbits, init=1, amplitude=512, noise_var=8, spb=8, delay=0, first_bit=0,
+                           det=None):
+        """TX (PRBS +-amplitude + CLT-GRNG * noise_var, tx.py:70-81) -> slicer (rx.py:28) -> detector."""
+        ctr = DetCounters()
+        x0 = state_words(init, self.n)
+        self._check(self._L.bbb_prbs_slicer_detect(self._h, k, first_bit, nbits, _ptr(x0, C.c_uint64), amplitude,
+                                                   noise_var, spb, delay,
+                                                   C.byref(det) if det is not None else None, C.byref(ctr)))
         return ctr.as_dict()
 
     def prbs_spec_state(self, k, first_bit, m=0, seed=1):

@@ -166,6 +166,21 @@ typedef struct {
  * are ADDED to *ctr. */
 int bbb_prbs_detect(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits, uint32_t err_m,
                     uint64_t seed, bbb_det_state *det, bbb_det_counters *ctr);
+/* Same generator and detector, channel errors supplied by the caller on the device:
+ * bit i of err_words_dev[j] set = PRBS bit first_bit + 64*j + i arrives inverted.  Replaces
+ * wiring an arbitrary error pattern into PRBSErrorDetector.bit as the reference's own test
+ * does (prbs.py:124-165).  ceil(nbits/64) words are read. */
+int bbb_prbs_detect_errs_dev(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits,
+                             const uint64_t *err_words_dev, bbb_det_state *det, bbb_det_counters *ctr);
+/* The board's noise loop without the pulse shaper: TX sample of bit b =
+ * (b ? +amplitude : -amplitude) + g * noise_var registered as a 12-bit signed word (tx.py:75-81),
+ * g = CLT-GRNG of the loaded recurrence from init x0 (tx.py:70-71), `spb` samples per bit; RX
+ * slices at zero (rx.py:28: sliced = ~sample[-1]), keeps sample `delay` of every bit
+ * (rx.py:31-32) and clocks PRBSErrorDetector with it (rx.py:43-46).  Bit i (absolute) uses noise
+ * sample g[i*spb + delay].  nbits must be a multiple of 64; `injected` counts the slicer errors. */
+int bbb_prbs_slicer_detect(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits, const uint64_t *x0,
+                           uint32_t amplitude, uint32_t noise_var, uint32_t spb, uint32_t delay,
+                           bbb_det_state *det, bbb_det_counters *ctr);
 /* The state a locked detector with no reload pending has just before bit first_bit (>= 64) of that
  * channel: what a shard that does not start at bit 0 passes as `det` before it has its left
  * neighbour's end state; the caller compares the two and re-runs the shard on a mismatch

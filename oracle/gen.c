@@ -276,3 +276,17 @@ void orc_prbs_detect(uint32_t k, uint32_t *gen_state, orc_det_state *det,
         ctr->reload_events += (o >> 2) & 1;
     }
 }
+
+void orc_det_run_bits(uint32_t k, orc_det_state *det, const uint64_t *rx, const uint64_t *tx,
+                      uint64_t nbits, orc_det_counters *ctr)
+{
+    for (uint64_t i = 0; i < nbits; i++) {
+        uint32_t bit = (uint32_t)((rx[i >> 6] >> (i & 63)) & 1);
+        uint32_t o = orc_det_clock(k, det, bit);
+        if (tx) ctr->injected += (uint32_t)((tx[i >> 6] >> (i & 63)) & 1) ^ bit;
+        ctr->err += o & 1;
+        ctr->err_valid += (o & 1) & !((o >> 1) & 1);
+        ctr->reload_cycles += (o >> 1) & 1;
+        ctr->reload_events += (o >> 2) & 1;
+    }
+}

@@ -91,6 +91,12 @@ void orc_prbs_detect(uint32_t k, uint32_t *gen_state, orc_det_state *det,
                      uint64_t first_bit, uint64_t nbits, uint32_t m, uint64_t seed,
                      orc_det_counters *ctr);
 
+/* The detector alone, clocked with nbits received bits (bit i = rx[i/64] >> i%64); `tx` (may be
+ * NULL) are the transmitted bits, used only to count `injected` = popcount(rx ^ tx).  This is how
+ * the reference's own test drives it (prbs.py:124-165: an arbitrary pattern wired into `bit`). */
+void orc_det_run_bits(uint32_t k, orc_det_state *det, const uint64_t *rx, const uint64_t *tx,
+                      uint64_t nbits, orc_det_counters *ctr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -122,6 +122,8 @@ def lib():
         "orc_err_word": (C.c_uint64, [C.c_uint64, C.c_uint64, C.c_uint32]),
         "orc_det_reset": (None, [C.c_uint32, P(DetState)]),
         "orc_det_clock": (C.c_uint32, [C.c_uint32, P(DetState), C.c_uint32]),
+        "orc_det_run_bits": (None, [C.c_uint32, P(DetState), P(C.c_uint64), P(C.c_uint64), C.c_uint64,
+                                    P(DetCounters)]),
         "orc_prbs_detect": (None, [C.c_uint32, u32p, P(DetState), C.c_uint64, C.c_uint64,
                                    C.c_uint32, C.c_uint64, P(DetCounters)]),
         "orc_rnghunt_candidate": (_BMat, [C.c_uint32, C.c_uint64, C.c_uint64]),
@@ -448,6 +450,34 @@ def prbs_detect(k, nbits, m=0, seed=1, first_bit=0, gen_state=None, det=None):
     ctr = DetCounters()
     L.orc_prbs_detect(k, C.byref(gs), C.byref(det), first_bit, nbits, m, seed, C.byref(ctr))
     return ctr.as_dict(), int(gs.value), det
+
+
+def det_run_bits(k, rx_words, nbits, tx_words=None, det=None):
+    """PRBSErrorDetector (prbs.py:43-99) clocked with caller-supplied received bits."""
+    L = lib()
+    if det is None:
+        det = DetState()
+        L.orc_det_reset(k, C.byref(det))
+    ctr = DetCounters()
+    rx = np.ascontiguousarray(rx_words, dtype=np.uint64)
+    tx = None if tx_words is None else np.ascontiguousarray(tx_words, dtype=np.uint64)
+    L.orc_det_run_bits(k, C.byref(det), _u64p(rx), _u64p(tx) if tx is not None else None, nbits, C.byref(ctr))
+    return ctr.as_dict(), det
+
+
+def slicer_rx_bits(tx_words, g, nbits, amplitude, noise_var, spb, delay):
+    """Received bits of the board's noise loop without the pulse shaper: TX sample of bit b =
+    (+-amplitude) + g*noise_var as a 12-bit signed register (tx.py:75-81), RX slices at zero
+    (rx.py:28: sliced = ~sample[-1]) and keeps sample `delay` of the spb samples of each bit.
+    g: int8 samples covering bit i at g[i*spb + delay]."""
+    tx = np.unpackbits(np.ascontiguousarray(tx_words, dtype="<u8").view(np.uint8), bitorder="little")[:nbits]
+    noise = g[delay::spb][:nbits].astype(np.int64) * int(noise_var)
+    x = np.where(tx == 1, int(amplitude), -int(amplitude)) + noise
+    x12 = ((x + 2048) & 4095) - 2048                    # Signal((12, True)), tx.py:80-81
+    rx = (x12 >= 0).astype(np.uint8)
+    pad = (-nbits) % 64
+    rxw = np.packbits(np.concatenate([rx, np.zeros(pad, np.uint8)]), bitorder="little").view("<u8")
+    return rxw.astype(np.uint64)
 
 
 def rnghunt_sweep(n, seed, first, count, threads=1):

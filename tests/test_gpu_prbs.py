@@ -180,3 +180,58 @@ def test_bad_arguments(ctx):
         ctx.prbs_stream(7, 64, state0=1 << 7)
     with pytest.raises(lib.BBBError):
         ctx.prbs_detect(7, 64, m=17)
+
+
+# ---- caller-supplied error words, and the TX noise -> slicer -> detector loop --------
+@pytest.mark.parametrize("k", [7, 15, 31])
+def test_detect_with_supplied_error_words(ctx, orc, k):
+    import torch
+    from basebandboard_b200 import lib
+    rng = np.random.default_rng(k)
+    nbits = (1 << 18) + 64 * 3
+    nw = nbits // 64
+    ew = np.zeros(nw, dtype=np.uint64)
+    hits = rng.integers(0, nbits, size=400)
+    for h in hits:
+        ew[h >> 6] |= np.uint64(1 << int(h & 63))
+    ew[nw // 2: nw // 2 + 3] = np.uint64(0xFFFFFFFFFFFFFFFF)      # a burst: forces reloads
+    first = 12345
+    tx, _ = orc.prbs_bits(k, nbits, state=orc.lib().orc_prbs_advance(k, 1, first))
+    want, wdet = orc.det_run_bits(k, tx ^ ew, nbits, tx_words=tx)
+    d_ew = torch.from_numpy(ew.view(np.int64)).cuda()
+    for chunk in (0, 32, 1000):
+        ctx.set_tuning("prbs_chunk_words", chunk)
+        det = lib.DetState(0, 1, (1 << k) - 1, 0)
+        got = ctx.prbs_detect_errs_dev(k, nbits, d_ew.data_ptr(), first_bit=first, det=det)
+        assert got == want, (k, chunk)
+        assert _same_det(det, wdet)
+    ctx.set_tuning("prbs_chunk_words", 0)
+    assert want["reload_events"] >= 2 and want["err_valid"] > 100
+
+
+@pytest.mark.parametrize("k,amp,nv,spb,delay", [(7, 300, 8, 8, 0), (15, 200, 15, 8, 5), (31, 900, 15, 4, 3),
+                                                (23, 64, 1, 1, 0), (9, 2047, 15, 2, 1)])
+def test_slicer_loop_matches_oracle(ctx, orc, k, amp, nv, spb, delay):
+    """PRBS -> (+-A + CLT-GRNG*noise_var, 12-bit) -> slicer -> PRBSErrorDetector (tx.py:70-81, rx.py:28-46)
+    == oracle composition, including chunked passes with detector hand-off."""
+    from basebandboard_b200 import lib, recurrences
+    ctx.lutopt_load_shipped(256)
+    first, nbits = 64 * 1000 + 17, 64 * 3000
+    g = orc.clt_run(recurrences.packed(256), 1, first * spb, nbits * spb, model=0, want=("out8",))["out8"]
+    tx, _ = orc.prbs_bits(k, nbits, state=orc.lib().orc_prbs_advance(k, 1, first))
+    rx = orc.slicer_rx_bits(tx, g, nbits, amp, nv, spb, delay)
+    want, wdet = orc.det_run_bits(k, rx, nbits, tx_words=tx)
+    for chunk_bits in (0, 64 * 700):
+        ctx.set_tuning("slicer_chunk_bits", chunk_bits)
+        det = lib.DetState(0, 1, (1 << k) - 1, 0)
+        got = ctx.prbs_slicer_detect(k, nbits, init=1, amplitude=amp, noise_var=nv, spb=spb, delay=delay,
+                                     first_bit=first, det=det)
+        assert got == want, (k, chunk_bits)
+        assert _same_det(det, wdet)
+    ctx.set_tuning("slicer_chunk_bits", 0)
+    if (k, amp) == (15, 200):
+        assert want["injected"] > 1000   # sigma = 8 * 15 = 120: a 1.7 sigma slicer margin
+    with pytest.raises(lib.BBBError):
+        ctx.prbs_slicer_detect(k, 100, spb=8)            # not a multiple of 64
+    with pytest.raises(lib.BBBError):
+        ctx.prbs_slicer_detect(k, 128, spb=3)

@@ -172,3 +172,28 @@ def test_error_word_rate():
     assert L.orc_err_word(1, 5, 0) == 0xFFFFFFFFFFFFFFFF
     ctr, _, _ = O.prbs_detect(15, 1 << 16, m=6, seed=1)
     assert ctr["injected"] > 500 and ctr["err"] >= ctr["err_valid"] > 0
+
+
+def test_detector_on_supplied_bits_equals_keyed_channel():
+    """orc_det_run_bits (the detector alone) fed with generator ^ keyed error words reproduces
+    orc_prbs_detect exactly; and the slicer model reduces to it: zero noise -> zero errors."""
+    L = O.lib()
+    for k, m in ((7, 3), (15, 6), (31, 4)):
+        nbits = 20000
+        tx, _ = O.prbs_bits(k, nbits)
+        ew = np.array([L.orc_err_word(1, w, m) for w in range((nbits + 63) // 64)], dtype=np.uint64)
+        want, _, wdet = O.prbs_detect(k, nbits, m=m, seed=1)
+        # the keyed channel injects only inside [0, nbits): mask the ragged tail the same way
+        tail = nbits % 64
+        if tail:
+            ew[-1] &= np.uint64((1 << tail) - 1)
+        got, gdet = O.det_run_bits(k, tx ^ ew, nbits, tx_words=tx)
+        assert got == want
+        assert (gdet.prbs, gdet.err_sr, gdet.reload_ctr, gdet.bit_in) == (wdet.prbs, wdet.err_sr, wdet.reload_ctr, wdet.bit_in)
+    tx, _ = O.prbs_bits(9, 640)
+    g = np.zeros(640 * 8, dtype=np.int8)
+    assert np.array_equal(O.slicer_rx_bits(tx, g, 640, 100, 8, 8, 3), tx)
+    # 12-bit wrap (tx.py:80-81): +2047 + 127*15 overflows to a negative word -> sliced 0
+    ones = np.full(10, 0xFFFFFFFFFFFFFFFF, dtype=np.uint64)
+    g = np.full(640, 127, dtype=np.int8)
+    assert int(O.slicer_rx_bits(ones, g, 640, 2047, 15, 1, 0).sum()) == 0
