@@ -52,6 +52,19 @@ def to_matrix_text(packed_rows):
     return "\n".join(lines) + "\n"
 
 
+def to_binary_matrix(packed_rows):
+    """Packed tap lists -> u64 words in the crate's BinaryMatrix layout (binary_matrix.rs:10-20):
+    column-major, word data[col*wpc + r//64], row r at bit 63 - r%64.  What bbb_rnghunt_eval takes."""
+    import numpy as np
+    n = len(packed_rows)
+    wpc = (n + 63) // 64
+    data = np.zeros(n * wpc, dtype=np.uint64)
+    for r, row in enumerate(packed_rows):
+        for c in row:
+            data[c * wpc + r // 64] |= np.uint64(1 << (63 - r % 64))
+    return data
+
+
 # names matching the reference module (rng_recurrences.py)
 n16, n32, n64, n128, n192, n256 = (packed(n) for n in (16, 32, 64, 128, 192, 256))
 n512 = packed(512)

@@ -206,6 +206,43 @@ def run_secondary(args, ctx, rank, world, local_rank):
                     "(BASELINE.json configs[1])" % (args.k, args.err_m, args.log2_bits))
         dtype = "u32/u64 integer"
         l2 = "no HBM-resident input"
+    elif w == "prbs_slicer":
+        # single-GPU composite; ranks run independent replicas of the same range
+        nbits = 1 << args.log2_bits
+        ctx.lutopt_load_shipped(N_STATE)
+        def step():
+            det = lib.DetState(0, 1, (1 << args.k) - 1, 0)
+            extra["ctr"] = ctx.prbs_slicer_detect(args.k, nbits, init=1, amplitude=args.amplitude, noise_var=args.noise_var,
+                                                  spb=args.spb, delay=0, det=det)
+            extra["rounds"] = ctx.last_rounds
+            return ctx.last_launches
+        def step_e2e():
+            step()
+            return nbits, ctx.last_h2d_bytes + 48, ctx.last_d2h_bytes
+        units, metric, unit, scale = nbits, "prbs_slicer_gbit_per_s", "Gbit/s", 1e-9
+        workload = ("PRBS-%d -> +-%d + CLT-GRNG(n256) x %d (12-bit TX word, %d samples/bit) -> slicer -> error detector, "
+                    "2^%d bits per GPU (SURVEY 8f-1; replicas, not shards)" % (args.k, args.amplitude, args.noise_var,
+                                                                            args.spb, args.log2_bits))
+        dtype = "u32 GF(2) + int8/int32"
+        l2 = "intermediate sample buffer (%d MiB per pass) exceeds L2" % ((min(nbits, 1 << 27) * args.spb) >> 20)
+    elif w == "clt_stream":
+        count = 1 << args.log2_samples
+        first = rank * count
+        ctx.lutopt_load_shipped(N_STATE)
+        eb = 2 if args.noise_var_stream >= 0 else 1
+        buf = torch.empty(count * eb, dtype=torch.uint8, device="cuda")
+        def step():
+            ctx.clt_stream_dev(1, first, count, 0, max(args.noise_var_stream, 1), buf.data_ptr(), eb)
+            return ctx.last_launches
+        def step_e2e():
+            n = min(count, 1 << 30)
+            ctx.clt_stream(1, first, n, model=0, noise_var=None if eb == 1 else args.noise_var_stream)
+            return n, ctx.last_h2d_bytes, ctx.last_d2h_bytes
+        units, metric, unit, scale = count, "clt_stream_gsamples_per_s", "Gsamples/s", 1e-9
+        workload = ("clt-grng n256 %s samples materialised to HBM, 2^%d samples/GPU (BASELINE.json configs[4])"
+                    % ("int8" if eb == 1 else "int16 x noise_var %d" % args.noise_var_stream, args.log2_samples))
+        dtype = "u32 (GF(2) bit ops)"
+        l2 = "output (%d MiB) exceeds L2; nothing is read back" % ((count * eb) >> 20)
     else:
         cnt = 1 << args.log2_candidates
         def step():
@@ -259,6 +296,12 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                 "frac": ach / hbm_peak, "traffic": None,
                                 "note": "algorithmic bytes = 1/8 B per PRBS bit; peak = measured copy bandwidth "
                                         "(MEASURED_PEAKS.json), per GPU"}
+        if w == "clt_stream":
+            # still integer-pipe bound when stored (30.8 thread-instr per byte), SURVEY 8d
+            line["roofline"] = {"bound": "alu", "achieved": value / world * 1e9 * 30.8125 / 1e12, "unit": "T thread-instr/s (LOP3-equivalent)",
+                                "peak": None, "frac": None, "traffic": None,
+                                "hbm_write_gbs": units * (2 if args.noise_var_stream >= 0 else 1) / (dev_ms / args.steps * 1e-3) / 1e9,
+                                "note": "986 LOP3 per 32 samples as for the fused kernel; HBM write rate given for reference"}
         if "ctr" in extra:
             line["result_check"] = dict(extra["ctr"], rounds=extra["rounds"])
         if "res" in extra:
@@ -279,12 +322,16 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--log2-samples", type=int, default=40)
     ap.add_argument("--workload", default="clt_fused",
-                    choices=["clt_fused", "prbs_stream", "prbs_detect", "rnghunt"],
+                    choices=["clt_fused", "prbs_stream", "prbs_detect", "rnghunt", "prbs_slicer", "clt_stream"],
                     help="clt_fused = the headline (BASELINE.json configs[2]); the others are the remaining "
                          "BASELINE configs, same JSON contract, their own metric")
     ap.add_argument("--k", type=int, default=31, help="PRBS order for the prbs_* workloads")
     ap.add_argument("--log2-bits", type=int, default=36, help="PRBS bits per GPU per step")
     ap.add_argument("--err-m", type=int, default=10, help="prbs_detect channel error probability 2^-m")
+    ap.add_argument("--amplitude", type=int, default=256, help="prbs_slicer: TX bit amplitude (12-bit word)")
+    ap.add_argument("--noise-var", type=int, default=8, help="prbs_slicer: noise_var 0..15 (tx.py:75-76; reset value 8)")
+    ap.add_argument("--spb", type=int, default=8, help="prbs_slicer: samples per bit (tx.py:36-37: data clock = 1/8)")
+    ap.add_argument("--noise-var-stream", type=int, default=-1, help="clt_stream: >= 0 stores int16 g*noise_var")
     ap.add_argument("--hunt-n", type=int, default=192)
     ap.add_argument("--log2-candidates", type=int, default=20, help="rnghunt candidates per GPU per step")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample length")
