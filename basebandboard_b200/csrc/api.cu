@@ -168,7 +168,7 @@ void bbb_destroy(bbb_ctx *c)
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (int i = 0; i < 12; i++) if (c->d_scratch[i]) cudaFree(c->d_scratch[i]);
+    for (int i = 0; i < 16; i++) if (c->d_scratch[i]) cudaFree(c->d_scratch[i]);
     if (c->d_row_ptr) cudaFree(c->d_row_ptr);
     if (c->d_taps) cudaFree(c->d_taps);
     bbb_prbs_free_tables(c);

@@ -79,8 +79,8 @@ struct bbb_ctx {
     uint16_t *d_taps = nullptr;
 
     // scratch device buffers (grown on demand)
-    void *d_scratch[12] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    size_t scratch_bytes[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    void *d_scratch[16] = {};
+    size_t scratch_bytes[16] = {};
 
     int fail(int code, const char *fmt, ...);
     int cuda_fail(cudaError_t e, const char *what);

@@ -737,3 +737,234 @@ int bbb_prbs_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t 
 }
 
 }  // extern "C"
+
+// ===========================================================================
+// Pulse shaper (gateware/bbb/bitshaper.py:12-91) and the full TX word (tx.py:52-81)
+// ===========================================================================
+// The HDL holds the last 8 PRBS bits in a shift register and, on each of the 8 clocks of a bit
+// period, sums 8 ROM words (+c or -c of one 64-tap pulse, selected by the register bit).  As a
+// sequence (the relation the reference test pins, bitshaper.py:150-163): y[8m+4] = 2 b[m] - 1, else 0;
+// S[t] = sum_k c[k] y[t-k]; the register resets to 0, i.e. b[m] = 0 (a -1 pulse) for m < 0.  The HDL's
+// 13-clock pipeline latency is dropped (the same convention as the CLT sample index).
+struct ShaperCoef { int16_t c[64]; };
+
+// PRBS bit J (absolute) from words that start at absolute bit `origin`; 0 before the start of time
+__device__ __forceinline__ uint32_t tx_bit(const uint64_t *__restrict__ w, int64_t J, int64_t origin)
+{
+    if (J < 0) return 0u;
+    const uint64_t r = (uint64_t)(J - origin);
+    return (uint32_t)(w[r >> 6] >> (r & 63)) & 1u;
+}
+
+// S[8J+p] for p = 0..7 from the 9 bits b[J-8] .. b[J] (win bit q = b[J-8+q])
+__device__ __forceinline__ void shaped8(const ShaperCoef &cf, uint32_t win, int32_t (&s)[8])
+{
+#pragma unroll
+    for (int p = 0; p < 8; p++) {
+        int32_t a = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            // p >= 4: tap 8i + p - 4 of bit J - i;  p < 4: tap 8i + p + 4 of bit J - 1 - i
+            const int k = p >= 4 ? 8 * i + p - 4 : 8 * i + p + 4;
+            const int q = p >= 4 ? 8 - i : 7 - i;
+            const int32_t c = cf.c[k];
+            a += ((win >> q) & 1u) ? c : -c;
+        }
+        s[p] = a;
+    }
+}
+
+// TX words x[t] = wrap12(bit_en * S[t] + g[t] * noise_var), t in [8*first_bit, 8*(first_bit+nbits)); one
+// thread per bit period: eight int16 = one 128-bit store.  g may be null (noise off).
+__global__ void __launch_bounds__(256)
+shaper_stream_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t first_bit, uint64_t nbits, ShaperCoef cf,
+                     uint32_t bit_en, const int8_t *__restrict__ g, int32_t noise_var, uint4 *__restrict__ out)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nbits) return;
+    const int64_t J = first_bit + (int64_t)r;
+    uint32_t win = 0;
+#pragma unroll
+    for (int q = 0; q < 9; q++) win |= tx_bit(txw, J - 8 + q, origin) << q;
+    int32_t s[8];
+    shaped8(cf, win, s);
+    uint32_t o[4];
+    uint2 gg = make_uint2(0u, 0u);
+    if (g) gg = *(const uint2 *)(g + r * 8);
+#pragma unroll
+    for (int p = 0; p < 8; p++) {
+        const int32_t nz = (int32_t)(int8_t)(((p < 4 ? gg.x : gg.y) >> (8 * (p & 3))) & 0xffu) * noise_var;
+        const int32_t x = (bit_en ? s[p] : 0) + nz;
+        const uint32_t x12 = (uint32_t)((((x + 2048) & 4095) - 2048)) & 0xffffu;
+        if (p & 1) o[p >> 1] |= x12 << 16;
+        else o[p >> 1] = x12;
+    }
+    __stcs(out + r, make_uint4(o[0], o[1], o[2], o[3]));
+}
+
+// RX decisions through the shaped channel: bit J is decided on the sample 8*(J+4)+delay (the pulse of
+// bit J peaks at tap 32), sliced at zero (rx.py:28); err word = decisions XOR transmitted bits.
+__global__ void __launch_bounds__(256)
+shaped_slicer_err_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t first_bit, uint64_t nwords, ShaperCoef cf,
+                         uint32_t delay, const int8_t *__restrict__ g, int32_t noise_var, uint64_t *__restrict__ err)
+{
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nwords) return;
+    uint64_t e = 0;
+    for (uint32_t i = 0; i < 64; i++) {
+        const uint64_t r = j * 64 + i;
+        const int64_t J = first_bit + (int64_t)r + 4;          // the bit period the sample lies in
+        uint32_t win = 0;
+#pragma unroll
+        for (int q = 0; q < 9; q++) win |= tx_bit(txw, J - 8 + q, origin) << q;
+        int32_t a = 0;
+#pragma unroll
+        for (int t = 0; t < 8; t++) {
+            const int k = delay >= 4 ? 8 * t + (int)delay - 4 : 8 * t + (int)delay + 4;
+            const int q = delay >= 4 ? 8 - t : 7 - t;
+            const int32_t c = cf.c[k];
+            a += ((win >> q) & 1u) ? c : -c;
+        }
+        const int32_t x = a + (int32_t)g[r * 8 + delay] * noise_var;
+        const int32_t x12 = ((x + 2048) & 4095) - 2048;
+        const uint32_t b = (win >> 4) & 1u;                    // b[J-4] = the bit being decided
+        e |= (uint64_t)((uint32_t)(x12 >= 0) ^ b) << i;
+    }
+    err[j] = e;
+}
+
+// PRBS words covering absolute bits [origin, last) on the device (scratch slot 10); origin = 64 bits
+// before `first` when there are that many
+static int shaper_tx_words(bbb_ctx *c, uint32_t k, uint64_t first, uint64_t nbits_with_lookahead, size_t extra_words,
+                           uint64_t **d_tx, int64_t *origin)
+{
+    const uint64_t org = first >= 64 ? first - 64 : 0;
+    const uint64_t span = ((first - org) + nbits_with_lookahead + 63) & ~63ull;
+    uint64_t *d = (uint64_t *)c->scratch(10, (size_t)(span / 64 + extra_words) * 8);
+    if (!d) return BBB_ECUDA;
+    int rc = bbb_prbs_stream_dev(c, k, 1u, org, span, d);
+    if (rc) return rc;
+    *d_tx = d;
+    *origin = (int64_t)org;
+    return BBB_OK;
+}
+
+static int shaper_check(bbb_ctx *c, const int16_t *coeff, ShaperCoef &cf)
+{
+    if (!coeff) return c->fail(BBB_EINVAL, "coeff is null");
+    for (int i = 0; i < 64; i++) {
+        if (coeff[i] <= -256 || coeff[i] > 255) return c->fail(BBB_EINVAL, "coefficients must lie in (-256, 255] (bitshaper.py:19-20)");
+        cf.c[i] = coeff[i];
+    }
+    return BBB_OK;
+}
+
+extern "C" {
+
+int bbb_tx_stream_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff, uint32_t bit_en,
+                      const uint64_t *x0, uint32_t noise_var, int16_t *out_dev)
+{
+    int rc = check_prbs_args(c, k, 0);
+    if (rc) return rc;
+    ShaperCoef cf;
+    rc = shaper_check(c, coeff, cf);
+    if (rc) return rc;
+    if (!out_dev || ((uintptr_t)out_dev & 15)) return c->fail(BBB_EINVAL, "out_dev must be 16-byte aligned");
+    if (noise_var > 15) return c->fail(BBB_EINVAL, "noise_var 0..15 (tx.py:49)");
+    if (x0 && (c->n == 0 || c->n > 256)) return c->fail(BBB_ESTATE, "load a recurrence with n <= 256 first");
+    if ((first_bit + nbits) >> 58) return c->fail(BBB_EINVAL, "bit range too large");
+    c->begin_call();
+    struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
+    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 27);
+    for (uint64_t off = 0; off < nbits; off += CH) {
+        const uint64_t nb = nbits - off < CH ? nbits - off : CH;
+        uint64_t *d_tx;
+        int64_t origin;
+        rc = shaper_tx_words(c, k, first_bit + off, nb, 0, &d_tx, &origin);
+        if (rc) return rc;
+        int8_t *d_g = nullptr;
+        if (x0) {
+            d_g = (int8_t *)c->scratch(9, (size_t)nb * 8);
+            if (!d_g) return BBB_ECUDA;
+            rc = bbb_clt_stream_dev(c, x0, (first_bit + off) * 8, nb * 8, BBB_MODEL_GATEWARE, 1u, d_g, nullptr);
+            if (rc) return rc;
+        }
+        shaper_stream_kernel<<<(uint32_t)((nb + 255) / 256), 256, 0, c->stream>>>(
+            d_tx, origin, (int64_t)(first_bit + off), nb, cf, bit_en, d_g, (int32_t)noise_var, (uint4 *)(out_dev + off * 8));
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+    }
+    c->last_kernel = "tx_stream";
+    c->nest--;
+    c->end_call();
+    c->nest++;
+    return BBB_OK;
+}
+
+int bbb_tx_stream(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff, uint32_t bit_en,
+                  const uint64_t *x0, uint32_t noise_var, int16_t *out)
+{
+    if (!c) return BBB_EINVAL;
+    if (!out) return c->fail(BBB_EINVAL, "out is null");
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    int16_t *d = (int16_t *)c->scratch(12, (size_t)nbits * 16 + 16);
+    if (!d) return BBB_ECUDA;
+    int rc = bbb_tx_stream_dev(c, k, first_bit, nbits, coeff, bit_en, x0, noise_var, d);
+    if (rc) return rc;
+    BBB_CUDA(c, c->d2h(out, d, (size_t)nbits * 16));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return BBB_OK;
+}
+
+int bbb_prbs_shaped_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff,
+                                  const uint64_t *x0, uint32_t noise_var, uint32_t delay, bbb_det_state *det,
+                                  bbb_det_counters *ctr)
+{
+    int rc = check_prbs_args(c, k, 0);
+    if (rc) return rc;
+    ShaperCoef cf;
+    rc = shaper_check(c, coeff, cf);
+    if (rc) return rc;
+    if (!ctr || !x0) return c->fail(BBB_EINVAL, "null argument");
+    if (nbits & 63) return c->fail(BBB_EINVAL, "nbits must be a multiple of 64");
+    if (noise_var > 15 || delay > 7) return c->fail(BBB_EINVAL, "noise_var 0..15, delay 0..7");
+    if (c->n == 0 || c->n > 256) return c->fail(BBB_ESTATE, "load a recurrence with n <= 256 first");
+    if ((first_bit + nbits) >> 58) return c->fail(BBB_EINVAL, "bit range too large");
+    bbb_det_state d0;
+    if (det) d0 = *det;
+    else { d0.bit_in = 0; d0.prbs = 1; d0.err_sr = (uint32_t)((1ull << k) - 1); d0.reload_ctr = 0; }
+    c->begin_call();
+    struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
+    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 27);
+    uint32_t rounds = 0;
+    for (uint64_t off = 0; off < nbits; off += CH) {
+        const uint64_t nb = nbits - off < CH ? nbits - off : CH, nw = nb / 64;
+        uint64_t *d_tx;
+        int64_t origin;
+        rc = shaper_tx_words(c, k, first_bit + off, nb + 64, nw, &d_tx, &origin);   // + the 4 bits after the range
+        if (rc) return rc;
+        const uint64_t span_words = (((first_bit + off) - (uint64_t)origin) + nb + 64 + 63) / 64;
+        uint64_t *d_err = d_tx + span_words;
+        int8_t *d_g = (int8_t *)c->scratch(9, (size_t)nb * 8);
+        if (!d_g) return BBB_ECUDA;
+        // the sample of bit J is 8*(J+4)+delay
+        rc = bbb_clt_stream_dev(c, x0, (first_bit + off + 4) * 8, nb * 8, BBB_MODEL_GATEWARE, 1u, d_g, nullptr);
+        if (rc) return rc;
+        shaped_slicer_err_kernel<<<(uint32_t)((nw + 255) / 256), 256, 0, c->stream>>>(
+            d_tx, origin, (int64_t)(first_bit + off), nw, cf, delay, d_g, (int32_t)noise_var, d_err);
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        rc = detect_impl(c, k, first_bit + off, nb, 0, 0, d_err, &d0, ctr);
+        if (rc) return rc;
+        rounds += c->last_rounds;
+    }
+    c->last_rounds = rounds;
+    c->last_kernel = "prbs_shaped_slicer_detect";
+    if (det) *det = d0;
+    c->nest--;
+    c->end_call();
+    c->nest++;
+    return BBB_OK;
+}
+
+}  // extern "C"

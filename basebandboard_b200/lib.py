@@ -82,6 +82,12 @@ SIGNATURES = {
                                            _P(DetState), _P(DetCounters)]),
     "bbb_prbs_slicer_detect": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, _u64p, C.c_uint32, C.c_uint32,
                                          C.c_uint32, C.c_uint32, _P(DetState), _P(DetCounters)]),
+    "bbb_tx_stream": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, _P(C.c_int16), C.c_uint32, _u64p, C.c_uint32,
+                                _P(C.c_int16)]),
+    "bbb_tx_stream_dev": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, _P(C.c_int16), C.c_uint32, _u64p,
+                                    C.c_uint32, C.c_void_p]),
+    "bbb_prbs_shaped_slicer_detect": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, _P(C.c_int16), _u64p,
+                                                C.c_uint32, C.c_uint32, _P(DetState), _P(DetCounters)]),
     "bbb_prbs_spec_state": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint32, C.c_uint64, _P(DetState)]),
     "bbb_last_rounds": (C.c_uint32, [_ctx]),
     "bbb_rnghunt_eval": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, _u64p, _u8p, _u64p]),
@@ -309,6 +315,32 @@ class Context:
         self._check(self._L.bbb_prbs_slicer_detect(self._h, k, first_bit, nbits, _ptr(x0, C.c_uint64), amplitude,
                                                    noise_var, spb, delay,
                                                    C.byref(det) if det is not None else None, C.byref(ctr)))
+        return ctr.as_dict()
+
+    def tx_stream(self, k, nbits, coeff, first_bit=0, bit_en=1, init=None, noise_var=0, dev_ptr=None):
+        """The 12-bit TX words (tx.py:52-81: shaped PRBS + CLT-GRNG * noise_var), 8 per bit, as int16.
+        init None = noise off.  dev_ptr: write to device memory instead of returning an array."""
+        cf = np.ascontiguousarray(coeff, dtype=np.int16)
+        assert cf.size == 64
+        x0 = state_words(init, self.n) if init is not None else None
+        px0 = _ptr(x0, C.c_uint64) if x0 is not None else None
+        if dev_ptr is not None:
+            self._check(self._L.bbb_tx_stream_dev(self._h, k, first_bit, nbits, _ptr(cf, C.c_int16), bit_en, px0,
+                                                  noise_var, C.c_void_p(dev_ptr)))
+            return None
+        out = np.zeros(nbits * 8, dtype=np.int16)
+        self._check(self._L.bbb_tx_stream(self._h, k, first_bit, nbits, _ptr(cf, C.c_int16), bit_en, px0, noise_var,
+                                          _ptr(out, C.c_int16)))
+        return out
+
+    def prbs_shaped_slicer_detect(self, k, nbits, coeff, init=1, noise_var=8, delay=4, first_bit=0, det=None):
+        """TX through the pulse shaper (bitshaper.py) + noise -> slicer at sample `delay` -> detector."""
+        ctr = DetCounters()
+        cf = np.ascontiguousarray(coeff, dtype=np.int16)
+        x0 = state_words(init, self.n)
+        self._check(self._L.bbb_prbs_shaped_slicer_detect(self._h, k, first_bit, nbits, _ptr(cf, C.c_int16),
+                                                          _ptr(x0, C.c_uint64), noise_var, delay,
+                                                          C.byref(det) if det is not None else None, C.byref(ctr)))
         return ctr.as_dict()
 
     def prbs_spec_state(self, k, first_bit, m=0, seed=1):

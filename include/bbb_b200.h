@@ -181,6 +181,25 @@ int bbb_prbs_detect_errs_dev(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint6
 int bbb_prbs_slicer_detect(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits, const uint64_t *x0,
                            uint32_t amplitude, uint32_t noise_var, uint32_t spb, uint32_t delay,
                            bbb_det_state *det, bbb_det_counters *ctr);
+/* ---- pulse shaper and the TX word (gateware/bbb/bitshaper.py, tx.py:52-81) ---- */
+/* PRBSShaper (bitshaper.py:12-91): coeff[64] is one pulse (each value in (-256, 255], 8 per bit
+ * duration; PRBSShaper.from_rcf builds the raised-cosine sets, basebandboard_b200/shaper.py restates
+ * it).  As a sequence, the relation the reference test pins (bitshaper.py:150-163):
+ * y[8m+4] = 2*b[m]-1 (else 0), S[t] = sum_k coeff[k]*y[t-k], b = PRBS-k from state 1, b[m<0] = 0 (the
+ * shift register's reset value); the HDL's 13-clock pipeline latency is dropped.
+ * out[t - 8*first_bit] = the 12-bit signed TX word (tx.py:80-81) x[t] = bit_en*S[t] + g[t]*noise_var,
+ * wrapped to 12 bits, stored as int16, for t in [8*first_bit, 8*(first_bit+nbits)); g = CLT-GRNG of
+ * the loaded recurrence from init x0 (x0 NULL = noise off). */
+int bbb_tx_stream(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff,
+                  uint32_t bit_en, const uint64_t *x0, uint32_t noise_var, int16_t *out);
+int bbb_tx_stream_dev(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff,
+                      uint32_t bit_en, const uint64_t *x0, uint32_t noise_var, int16_t *out_dev);
+/* bbb_prbs_slicer_detect through the shaped channel (inter-symbol interference included): bit J
+ * is decided on the sliced TX word x[8*(J+4) + delay] (its pulse peaks at tap 32), delay 0..7
+ * (rx.py:18-19), and the decisions clock PRBSErrorDetector.  `injected` = wrong decisions. */
+int bbb_prbs_shaped_slicer_detect(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits,
+                                  const int16_t *coeff, const uint64_t *x0, uint32_t noise_var, uint32_t delay,
+                                  bbb_det_state *det, bbb_det_counters *ctr);
 /* The state a locked detector with no reload pending has just before bit first_bit (>= 64) of that
  * channel: what a shard that does not start at bit 0 passes as `det` before it has its left
  * neighbour's end state; the caller compares the two and re-runs the shard on a mismatch

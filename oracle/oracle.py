@@ -480,6 +480,25 @@ def slicer_rx_bits(tx_words, g, nbits, amplitude, noise_var, spb, delay):
     return rxw.astype(np.uint64)
 
 
+def shaper_stream(tx_bits, coeff):
+    """PRBSShaper as a sequence (bitshaper.py:12-91; the relation its test pins at :150-163):
+    y[8m+4] = 2 b[m] - 1 else 0, S = lfilter(coeff, 1, y), with b[m] = 0 (-1 pulses) for the 8 bit
+    periods before tx_bits[0] unless the caller passes history.  tx_bits: 0/1 array whose FIRST 8
+    entries are the history b[first-8 .. first-1]; returns S[8*first .. ) for the remaining bits."""
+    b = np.asarray(tx_bits, dtype=np.int64)
+    y = np.zeros(8 * b.size, dtype=np.int64)
+    y[4::8] = 2 * b - 1
+    c = np.asarray(coeff, dtype=np.int64)
+    f = np.convolve(y, c)[: y.size]
+    return f[64:]
+
+
+def tx_words(shaped, g, noise_var, bit_en=1):
+    """tx.py:75-81: x = bitmux + noisemux registered as Signal((12, True)) -> wraps to 12 bits."""
+    x = (np.asarray(shaped, dtype=np.int64) if bit_en else 0) + np.asarray(g, dtype=np.int64) * int(noise_var)
+    return (((x + 2048) & 4095) - 2048).astype(np.int16)
+
+
 def rnghunt_sweep(n, seed, first, count, threads=1):
     stages = np.zeros(count, dtype=np.uint8)
     counts = np.zeros(5, dtype=np.uint64)
