@@ -410,11 +410,14 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
         }
 
         // ---- data-driven kernel: S streams of L = 2^k clocks ----
+        // short ranges (the ragged tails of the specialised launches): a clock of this kernel costs tens of
+        // microseconds whatever the grid, so fill the GPU with streams before adding clocks per stream;
+        // long ranges: 64 clocks or more per stream, up to 8 waves of streams
         uint32_t logL = 0;
-        if (rem >= Lmin) {
-            logL = 6;
+        while (logL < 6 && (rem >> (logL + 1)) >= Sres / 2) logL++;
+        if (logL == 6)
             while (logL < 40 && (rem >> logL) > 8 * Sres) logL++;
-        }
+        (void)Lmin;
         const uint64_t L = 1ull << logL;
         const uint64_t S = rem >> logL;                     // >= 1
         const uint64_t T64 = (S + 31) / 32;

@@ -482,6 +482,77 @@ clt256_words_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
     }
 }
 
+// One-pass variant of the raw-word kernel (tools/gen_clt256_v2.py, kind "words"): the one-pass clock without
+// the popcount network; then the NEW state is un-sliced 32 planes at a time (32x32 register transposes,
+// two PRMT stages + three shift/LOP3 stages) into a thread-private shared-memory stage [stream][word],
+// and every stream's 8 words leave as one complete 32-byte sector (two adjacent 128-bit stores).  The
+// two-pass kernel stored the two halves of a sector from different passes: 606 k half-written sectors
+// in flight, each costing a DRAM read-modify-write (ncu: 28 % ALU, 3 long-scoreboard stalls per issue).
+// One CTA per SM: state 76 KB + stage 128 KB.
+#define CLT256V2W_STAGE_WORDS (32 * 8 * CLT256V2_B)
+#define CLT256V2W_SMEM (CLT256V2_STATE_BYTES + CLT256V2W_STAGE_WORDS * 4)
+
+#define CLT256V2_W_EMIT(w, r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18, r19, \
+                        r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31)                                  \
+    {                                                                                                                \
+        uint32_t tw[32] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18,       \
+                           r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31};                          \
+        transpose32_fast(tw);                                                                                        \
+        _Pragma("unroll") for (int j = 0; j < 32; j++)                                                               \
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(stage_a + (uint32_t)((j * 8 + (w)) * CLT256V2_B * 4)), "r"(tw[j])); \
+    }
+
+#ifndef CLT256V2W_STORE_KIND
+#define CLT256V2W_STORE_KIND 0
+#endif
+#if CLT256V2W_STORE_KIND == 0
+#define CLT256V2W_STORE(p, v) __stcs(p, v)
+#elif CLT256V2W_STORE_KIND == 1
+#define CLT256V2W_STORE(p, v) (*(p) = (v))
+#else
+__device__ __forceinline__ void st_evict_last(uint4 *p, uint4 v)
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w),
+                 "l"(pol) : "memory");
+}
+#define CLT256V2W_STORE(p, v) st_evict_last(p, v)
+#endif
+
+__global__ void __launch_bounds__(CLT256V2_B, 1)
+clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+    uint32_t *const st = (uint32_t *)smem4 + tid;
+    for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+    const uint32_t stage_a = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES) + tid * 4u;
+    uint32_t *const outp = out + (size_t)t * 32u * L * 8u;   // stream j, clock it: outp + (j*L + it)*8
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_W_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_W_BODY
+        uint32_t *const o32 = outp + (size_t)it * 8u;
+#pragma unroll 4
+        for (int j = 0; j < 32; j++) {
+            uint32_t v[8];
+#pragma unroll
+            for (int w = 0; w < 8; w++)
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[w]) : "r"(stage_a + (uint32_t)((j * 8 + w) * CLT256V2_B * 4)));
+            uint4 *const d = (uint4 *)(o32 + (size_t)j * L * 8u);
+            CLT256V2W_STORE(d, make_uint4(v[0], v[1], v[2], v[3]));
+            CLT256V2W_STORE(d + 1, make_uint4(v[4], v[5], v[6], v[7]));
+        }
+    }
+}
+
 // kind: 1 = int8 samples, 2 = raw words, 3 = int16 scaled samples
 int bbb_clt_spec_stream_ok(const bbb_ctx *c, int kind)
 {
@@ -512,6 +583,11 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
                                                                              (int32_t)noise_var);
         c->last_kernel = "clt256_s16";
+    } else if (c->tune_spec_variant != 1) {
+        static_assert(CLT256V2W_SMEM <= 227 * 1024, "shared memory budget");
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_words2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2W_SMEM));
+        clt256_words2_kernel<<<blocks, CLT256V2_B, CLT256V2W_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
+        c->last_kernel = "clt256_words2";
     } else {
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          CLT256_STATE_BYTES));

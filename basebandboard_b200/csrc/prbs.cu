@@ -775,31 +775,65 @@ __device__ __forceinline__ void shaped8(const ShaperCoef &cf, uint32_t win, int3
 }
 
 // TX words x[t] = wrap12(bit_en * S[t] + g[t] * noise_var), t in [8*first_bit, 8*(first_bit+nbits)); one
-// thread per bit period: eight int16 = one 128-bit store.  g may be null (noise off).
+// thread per bit period: eight int16 = one 128-bit streaming store.  g may be null (noise off).
+// The eight sums of a bit period depend on 8 of the 9 window bits each (phases 0..3 on b[J-8..J-1],
+// phases 4..7 on b[J-7..J]), so a CTA first tabulates them: T2[pp][idx] = the sums of phases 2pp and
+// 2pp+1 as a packed int16 pair for every 8-bit pattern (4 KB of shared memory, 8 adds per entry).  A
+// bit period is then 4 LDS.32 and one store: the kernel is bound by HBM writes, not by the ALU.
 __global__ void __launch_bounds__(256)
 shaper_stream_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t first_bit, uint64_t nbits, ShaperCoef cf,
                      uint32_t bit_en, const int8_t *__restrict__ g, int32_t noise_var, uint4 *__restrict__ out)
 {
-    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= nbits) return;
-    const int64_t J = first_bit + (int64_t)r;
-    uint32_t win = 0;
+    __shared__ uint32_t T2[4][256];
+    for (uint32_t e = threadIdx.x; e < 1024; e += blockDim.x) {
+        const uint32_t pp = e >> 8, idx = e & 255u;
+        uint32_t pair = 0;
 #pragma unroll
-    for (int q = 0; q < 9; q++) win |= tx_bit(txw, J - 8 + q, origin) << q;
-    int32_t s[8];
-    shaped8(cf, win, s);
-    uint32_t o[4];
-    uint2 gg = make_uint2(0u, 0u);
-    if (g) gg = *(const uint2 *)(g + r * 8);
+        for (int h = 0; h < 2; h++) {
+            const int p = 2 * (int)pp + h;
+            int32_t a = 0;
 #pragma unroll
-    for (int p = 0; p < 8; p++) {
-        const int32_t nz = (int32_t)(int8_t)(((p < 4 ? gg.x : gg.y) >> (8 * (p & 3))) & 0xffu) * noise_var;
-        const int32_t x = (bit_en ? s[p] : 0) + nz;
-        const uint32_t x12 = (uint32_t)((((x + 2048) & 4095) - 2048)) & 0xffffu;
-        if (p & 1) o[p >> 1] |= x12 << 16;
-        else o[p >> 1] = x12;
+            for (int i = 0; i < 8; i++) {
+                // p >= 4: tap 8i + p - 4 of bit J - i;  p < 4: tap 8i + p + 4 of bit J - 1 - i; pattern bit 7 - i
+                const int k = p >= 4 ? 8 * i + p - 4 : 8 * i + p + 4;
+                const int32_t c = cf.c[k];
+                a += ((idx >> (7 - i)) & 1u) ? c : -c;
+            }
+            pair |= ((uint32_t)a & 0xffffu) << (16 * h);
+        }
+        T2[pp][idx] = pair;
     }
-    __stcs(out + r, make_uint4(o[0], o[1], o[2], o[3]));
+    __syncthreads();
+    // grid-stride over bit periods: the table is built once per CTA, stores stay coalesced
+    for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < nbits; r += (uint64_t)gridDim.x * blockDim.x) {
+        const int64_t J = first_bit + (int64_t)r;
+        uint32_t win = 0;                         // bit q = b[J-8+q]
+        if (J >= 8) {
+            const uint64_t a = (uint64_t)(J - 8 - origin);
+            const uint32_t sh = (uint32_t)(a & 63);
+            uint64_t w = txw[a >> 6] >> sh;
+            if (sh > 55) w |= txw[(a >> 6) + 1] << (64 - sh);
+            win = (uint32_t)w & 0x1ffu;
+        } else {
+#pragma unroll
+            for (int q = 0; q < 9; q++) win |= tx_bit(txw, J - 8 + q, origin) << q;
+        }
+        const uint32_t lo = win & 255u, hi = win >> 1;
+        uint32_t o[4] = {T2[0][lo], T2[1][lo], T2[2][hi], T2[3][hi]};
+        if (g || !bit_en) {
+            uint2 gg = make_uint2(0u, 0u);
+            if (g) gg = *(const uint2 *)(g + r * 8);
+#pragma unroll
+            for (int p = 0; p < 8; p++) {
+                const int32_t sp = bit_en ? (int32_t)(int16_t)(o[p >> 1] >> (16 * (p & 1))) : 0;
+                const int32_t nz = (int32_t)(int8_t)(((p < 4 ? gg.x : gg.y) >> (8 * (p & 3))) & 0xffu) * noise_var;
+                const int32_t x = sp + nz;
+                const uint32_t x12 = (uint32_t)((((x + 2048) & 4095) - 2048)) & 0xffffu;
+                o[p >> 1] = (p & 1) ? (o[p >> 1] & 0xffffu) | (x12 << 16) : (o[p >> 1] & 0xffff0000u) | x12;
+            }
+        }
+        __stcs(out + r, make_uint4(o[0], o[1], o[2], o[3]));
+    }
 }
 
 // RX decisions through the shaped channel: bit J is decided on the sample 8*(J+4)+delay (the pulse of
@@ -875,7 +909,9 @@ int bbb_tx_stream_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits
     if ((first_bit + nbits) >> 58) return c->fail(BBB_EINVAL, "bit range too large");
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
-    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 27);
+    // noise on: 2^27 bits per pass bounds the int8 sample buffer at 1 GiB; noise off: the packed PRBS words
+    // are the only intermediate (1/128 of the output), 2^32 bits per pass
+    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (x0 ? (1ull << 27) : (1ull << 32));
     for (uint64_t off = 0; off < nbits; off += CH) {
         const uint64_t nb = nbits - off < CH ? nbits - off : CH;
         uint64_t *d_tx;
@@ -889,7 +925,8 @@ int bbb_tx_stream_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits
             rc = bbb_clt_stream_dev(c, x0, (first_bit + off) * 8, nb * 8, BBB_MODEL_GATEWARE, 1u, d_g, nullptr);
             if (rc) return rc;
         }
-        shaper_stream_kernel<<<(uint32_t)((nb + 255) / 256), 256, 0, c->stream>>>(
+        const uint64_t want_blocks = (nb + 255) / 256, max_blocks = (uint64_t)c->sm_count * 16;
+        shaper_stream_kernel<<<(uint32_t)(want_blocks < max_blocks ? want_blocks : max_blocks), 256, 0, c->stream>>>(
             d_tx, origin, (int64_t)(first_bit + off), nb, cf, bit_en, d_g, (int32_t)noise_var, (uint4 *)(out_dev + off * 8));
         c->last_launches++;
         BBB_CUDA(c, cudaGetLastError());

@@ -225,6 +225,24 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                                                             args.spb, args.log2_bits))
         dtype = "u32 GF(2) + int8/int32"
         l2 = "intermediate sample buffer (%d MiB per pass) exceeds L2" % ((min(nbits, 1 << 27) * args.spb) >> 20)
+    elif w == "tx_stream":
+        from basebandboard_b200 import shaper
+        nbits = 1 << (args.log2_bits - 7)                 # 16 B per bit: 2^36 "bits" of budget = 8 GiB of TX words
+        first = rank * nbits
+        coeff = shaper.tx_sets()[16]
+        buf = torch.empty(nbits * 8, dtype=torch.int16, device="cuda")
+        def step():
+            ctx.tx_stream(args.k, nbits, coeff, first_bit=first, dev_ptr=buf.data_ptr())
+            return ctx.last_launches
+        def step_e2e():
+            n = min(nbits, 1 << 26)
+            ctx.tx_stream(args.k, n, coeff, first_bit=first)
+            return n * 16, ctx.last_h2d_bytes, ctx.last_d2h_bytes
+        units, metric, unit, scale = nbits * 16, "tx_stream_gbytes_per_s", "GB/s", 1e-9
+        workload = ("shaped PRBS-%d TX words (PRBSShaper set 16, noise off), 8 int16 per bit materialised to HBM, "
+                    "2^%d bits/GPU (SURVEY 8f-3)" % (args.k, args.log2_bits - 7))
+        dtype = "int16 sums of 9-bit coefficients"
+        l2 = "output (%d MiB) exceeds L2; nothing is read back" % ((nbits * 16) >> 20)
     elif w == "clt_stream":
         count = 1 << args.log2_samples
         first = rank * count
@@ -290,6 +308,11 @@ def run_secondary(args, ctx, rank, world, local_rank):
                 "e2e": {"value": world * e_units / (e2e_ms * 1e-3) * scale, "unit": unit,
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
                 "gpu_launches": launches}
+        if w == "tx_stream" and hbm_peak:
+            ach = units / (dev_ms / args.steps * 1e-3) / 1e9
+            line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                                "traffic": None, "note": "algorithmic bytes = 16 B written per PRBS bit (8 int16 TX words); "
+                                "peak = measured copy bandwidth (MEASURED_PEAKS.json), per GPU"}
         if w == "prbs_stream" and hbm_peak:
             ach = units / 8 / (dev_ms / args.steps * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
@@ -304,6 +327,19 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                 "note": "986 LOP3 per 32 samples as for the fused kernel; HBM write rate given for reference"}
         if "ctr" in extra:
             line["result_check"] = dict(extra["ctr"], rounds=extra["rounds"])
+        if w == "rnghunt":
+            # dominant kernel hunt_front: one shared-memory gather per tap per clock (2n clocks per candidate)
+            from basebandboard_b200 import recurrences as _rec
+            n_ = args.hunt_n
+            taps_per_cand = 2.0 * n_ * (n_ * 31.0 / 8.0)          # row weights [3,4,4,4,4,4,4,4]: 31/8 taps per row
+            sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+            lsu_peak = sm * 32 * clocks.get("sm_mhz", 1965) * 1e6 / 1e12
+            ach = value / world * taps_per_cand / 1e12
+            line["roofline"] = {"bound": "lsu", "kernel": "hunt_front", "achieved": ach, "peak": lsu_peak,
+                                "unit": "T shared-memory lane-loads/s", "frac": ach / lsu_peak, "traffic": None,
+                                "note": "algorithmic work = 2n clocks x 31n/8 tap gathers per candidate (binary_matrix.rs:68-76); "
+                                        "peak = one 32-lane LDS per SM per clock at the sampled SM clock; stores, "
+                                        "Berlekamp-Massey and the primitivity stage are not counted as algorithmic"}
         if "res" in extra:
             line["result_check"] = {"best": extra["res"]["best"],
                                     "stage_counts": [int(v) for v in extra["res"]["stage_counts"]]}
@@ -322,7 +358,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--log2-samples", type=int, default=40)
     ap.add_argument("--workload", default="clt_fused",
-                    choices=["clt_fused", "prbs_stream", "prbs_detect", "rnghunt", "prbs_slicer", "clt_stream"],
+                    choices=["clt_fused", "prbs_stream", "prbs_detect", "rnghunt", "prbs_slicer", "clt_stream", "tx_stream"],
                     help="clt_fused = the headline (BASELINE.json configs[2]); the others are the remaining "
                          "BASELINE configs, same JSON contract, their own metric")
     ap.add_argument("--k", type=int, default=31, help="PRBS order for the prbs_* workloads")
@@ -357,8 +393,9 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
+        # keep stdout to the one JSON line: NCCL writes its version banner (level VERSION and above) to
+        # stdout unless told otherwise
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = lib.Context(local_rank)
     for kv in args.tune:

@@ -219,9 +219,12 @@ def test_spec256_int8_stream_matches_oracle(ctx, orc, blocks, min_steps, count, 
         ctx.set_tuning("clt_spec_variant", 2)
 
 
+@pytest.mark.parametrize("variant", [1, 2])
 @pytest.mark.parametrize("blocks,min_steps,count,first", [(1, 8, 4096 * 9 + 5, 0), (2, 8, 2 * 4096 * 11 + 3, (1 << 35) + 1)])
-def test_spec256_word_stream_matches_oracle(ctx, orc, blocks, min_steps, count, first):
+def test_spec256_word_stream_matches_oracle(ctx, orc, blocks, min_steps, count, first, variant):
+    """raw URNG words: two-pass clt256_words and one-pass clt256_words2 (+ generic tail) == oracle"""
     ctx.lutopt_load_shipped(256)
+    ctx.set_tuning("clt_spec_variant", variant)
     ctx.set_tuning("clt_spec_min_steps", min_steps)
     ctx.set_tuning("clt_spec_max_blocks", blocks)
     try:
@@ -231,6 +234,7 @@ def test_spec256_word_stream_matches_oracle(ctx, orc, blocks, min_steps, count, 
     finally:
         ctx.set_tuning("clt_spec_min_steps", 512)
         ctx.set_tuning("clt_spec_max_blocks", 0)
+        ctx.set_tuning("clt_spec_variant", 2)
 
 
 def test_spec256_streams_equal_generic_large(ctx):

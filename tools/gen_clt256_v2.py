@@ -173,7 +173,7 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
         for b in rows[r]:
             taps_at[pos[b]].append(r)
     hooks = rmw_hooks_v2() if kind == "hist" else {}
-    tail, tail_ops = tail_lines(shape, kind) if shape is not None else ([], {})
+    tail, tail_ops = tail_lines(shape, kind) if (shape is not None and kind != "words") else ([], {})
     per_step = -(-len(tail) // TAIL_STEPS) if tail else 0
     heap = BitHeap(em)
     pending = {r: [] for r in range(N)}       # raw planes not yet folded
@@ -217,8 +217,9 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
         for ln in hooks.get(t, []):
             em.emit(ln)
         w = wexpr(t)
-        heap.add(w, parity(perm[t]) == 1)
-        heap.reduce()
+        if kind != "words":
+            heap.add(w, parity(perm[t]) == 1)
+            heap.reduce()
         for r in taps_at[t]:
             pending[r].append(w)
             left[r] -= 1
@@ -243,6 +244,15 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
     assert not store_at, store_at
     assert not tail
     assert assigned == set(resident)
+    if kind == "words":
+        # raw URNG words: the state AFTER the clock, un-sliced 32 planes at a time (resident planes from
+        # their registers, the others from their slots, where the clock has just stored them)
+        for wd in range(N // 32):
+            src = []
+            for b in range(32 * wd, 32 * wd + 32):
+                src.append(("r%d" % b) if b in resident else "st[%d * CLT256V2_B]" % slot_of[pos[b]])
+            em.emit("CLT256V2_W_EMIT(%d, %s)" % (wd, ", ".join(src)))
+        return em, perm
     new_shape = [[neg for _, neg in heap.heap[w]] for w in range(10)]
     if shape is None:
         return new_shape
@@ -265,6 +275,7 @@ def main():
     init = carried_init(shape)
     tail, _ = tail_lines(shape)
     em8, _ = body_hist_v2(rows, pos, resident, shape, "s8")
+    emw, _ = body_hist_v2(rows, pos, resident, shape, "words")
     tail8, _ = tail_lines(shape, "s8")
     out = os.path.join(ROOT, "basebandboard_b200", "csrc", "clt256_v2_gen.inc")
     with open(out, "w") as f:
@@ -290,6 +301,8 @@ def main():
         f.write("\n".join(em8.lines))
         f.write("\n#endif\n#ifdef CLT256V2_SECTION_S8_TAIL\n")
         f.write("\n".join(tail8))
+        f.write("\n#endif\n#ifdef CLT256V2_SECTION_W_BODY\n// same clock without the popcount network, then the new state as raw URNG words (rng.py:27)\n")
+        f.write("\n".join(emw.lines))
         f.write("\n#endif\n")
     print("wrote", out, "ops", em.ops, "peak live", peak, "resident", len(resident), file=sys.stderr)
 
