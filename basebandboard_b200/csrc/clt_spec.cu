@@ -546,9 +546,15 @@ clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #pragma unroll
             for (int w = 0; w < 8; w++)
                 asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[w]) : "r"(stage_a + (uint32_t)((j * 8 + w) * CLT256V2_B * 4)));
+#ifdef CLT256V2W_COALESCED_EXPERIMENT   /* wrong layout, same bytes: what the store pattern costs */
+            uint4 *const d0 = (uint4 *)out + ((size_t)(it * 32u + j) * 2u) * T + t;
+            CLT256V2W_STORE(d0, make_uint4(v[0], v[1], v[2], v[3]));
+            CLT256V2W_STORE(d0 + T, make_uint4(v[4], v[5], v[6], v[7]));
+#else
             uint4 *const d = (uint4 *)(o32 + (size_t)j * L * 8u);
             CLT256V2W_STORE(d, make_uint4(v[0], v[1], v[2], v[3]));
             CLT256V2W_STORE(d + 1, make_uint4(v[4], v[5], v[6], v[7]));
+#endif
         }
     }
 }
