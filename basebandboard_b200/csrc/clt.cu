@@ -47,8 +47,16 @@ seed_kernel(const uint32_t *__restrict__ J,   // [nbits][n][NW32] column-major j
             const uint32_t col = (uint32_t)k * 32u + lane;
             if (col < n && ((y[k] >> lane) & 1u)) {
                 const uint32_t *cp = Jb + (size_t)col * NW32;
+                if constexpr (NW32 % 4 == 0) {
 #pragma unroll
-                for (int w = 0; w < NW32; w++) acc[w] ^= __ldg(cp + w);
+                    for (int w = 0; w < NW32; w += 4) {
+                        const uint4 v = __ldg((const uint4 *)(cp + w));
+                        acc[w] ^= v.x; acc[w + 1] ^= v.y; acc[w + 2] ^= v.z; acc[w + 3] ^= v.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int w = 0; w < NW32; w++) acc[w] ^= __ldg(cp + w);
+                }
             }
         }
 #pragma unroll

@@ -707,7 +707,7 @@ int bbb_prbs_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t 
     else { d0.bit_in = 0; d0.prbs = 1; d0.err_sr = (uint32_t)((1ull << k) - 1); d0.reload_ctr = 0; }
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
-    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 27);
+    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 29);   // 4 GiB of int8 samples per pass
     uint32_t rounds = 0;
     for (uint64_t off = 0; off < nbits; off += CH) {
         const uint64_t nb = nbits - off < CH ? nbits - off : CH, nw = nb / 64;
@@ -909,9 +909,9 @@ int bbb_tx_stream_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits
     if ((first_bit + nbits) >> 58) return c->fail(BBB_EINVAL, "bit range too large");
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
-    // noise on: 2^27 bits per pass bounds the int8 sample buffer at 1 GiB; noise off: the packed PRBS words
+    // noise on: 2^29 bits per pass bounds the int8 sample buffer at 4 GiB; noise off: the packed PRBS words
     // are the only intermediate (1/128 of the output), 2^32 bits per pass
-    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (x0 ? (1ull << 27) : (1ull << 32));
+    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (x0 ? (1ull << 29) : (1ull << 32));
     for (uint64_t off = 0; off < nbits; off += CH) {
         const uint64_t nb = nbits - off < CH ? nbits - off : CH;
         uint64_t *d_tx;
@@ -972,7 +972,7 @@ int bbb_prbs_shaped_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, ui
     else { d0.bit_in = 0; d0.prbs = 1; d0.err_sr = (uint32_t)((1ull << k) - 1); d0.reload_ctr = 0; }
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
-    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 27);
+    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 29);   // 4 GiB of int8 samples per pass
     uint32_t rounds = 0;
     for (uint64_t off = 0; off < nbits; off += CH) {
         const uint64_t nb = nbits - off < CH ? nbits - off : CH, nw = nb / 64;

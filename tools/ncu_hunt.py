@@ -1,10 +1,7 @@
-#!/usr/bin/env python3
-"""One rnghunt sweep of 2^16 candidates at n = 192, for ncu."""
-import os
-import sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from basebandboard_b200 import lib  # noqa: E402
+import os, sys
+sys.path.insert(0, "/root/repo")
+from basebandboard_b200 import lib
 c = lib.Context(0)
-r = c.rnghunt_sweep(192, 1, 0, 1 << 16, k=16)
-print(r["best"][:4], c.last_device_ms)
+r = c.rnghunt_sweep(192, 1, 0, 1 << 18, k=16)
+print(c.last_kernel, c.last_device_ms, r["best"][:3])
 c.close()
