@@ -139,7 +139,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit_json(line)
 
 
 def workload_config(args, world):
@@ -343,14 +343,38 @@ def run_secondary(args, ctx, rank, world, local_rank):
         if "res" in extra:
             line["result_check"] = {"best": extra["res"]["best"],
                                     "stage_counts": [int(v) for v in extra["res"]["stage_counts"]]}
-        print(json.dumps(line), flush=True)
+        emit_json(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version
+    banner to stdout at NCCL_DEBUG=VERSION/WARN), so file descriptor 1 is pointed at stderr for the
+    whole run and the JSON line goes to a saved duplicate of the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_json(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -501,7 +525,7 @@ def main():
             rate = cpu_port_rate(n_cpu, cores)
             line["cpu_baseline"] = {"value": rate / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": "first %d samples of the workload (oracle/gen.c, %d threads)" % (n_cpu, cores)}
-        print(json.dumps(line), flush=True)
+        emit_json(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
