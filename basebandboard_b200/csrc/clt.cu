@@ -32,7 +32,7 @@ seed_kernel(const uint32_t *__restrict__ J,   // [nbits][n][NW32] column-major j
     const uint32_t s = gw * 32 + lane;   // stream index
     // The warp works on ONE state at a time, replicated in every lane: a jump operator is applied
     // cooperatively (lane l folds columns l, l+32, ... -- coalesced reads of the column-major operator --
-    // then an XOR butterfly leaves the product in all lanes).  First the bits of the stream index the
+    // then a warp-wide XOR reduction (REDUX) leaves the product in all lanes).  First the bits of the stream index the
     // whole warp shares (b >= 5), then 31 successive applications of J[0] = A^L; lane l keeps the state
     // after l of them: A^(s*L) x with s = 32*gw + l.
     uint32_t y[NW32], x[NW32];
@@ -60,11 +60,7 @@ seed_kernel(const uint32_t *__restrict__ J,   // [nbits][n][NW32] column-major j
             }
         }
 #pragma unroll
-        for (int off = 16; off >= 1; off >>= 1)
-#pragma unroll
-            for (int w = 0; w < NW32; w++) acc[w] ^= __shfl_xor_sync(0xffffffffu, acc[w], off);
-#pragma unroll
-        for (int w = 0; w < NW32; w++) y[w] = acc[w];
+        for (int w = 0; w < NW32; w++) y[w] = __reduce_xor_sync(0xffffffffu, acc[w]);   // REDUX.XOR: one instruction per word
     };
     for (uint32_t b = 5; b < nbits; b++)
         if ((gw >> (b - 5)) & 1u) apply(J + (size_t)b * n * NW32);
