@@ -139,12 +139,25 @@ static __device__ __noinline__ void clt256v2_slow(uint32_t p0, uint32_t p1, uint
 #define CLT256V2_AFTER_COUNT(p0, p1, p2, p3, p4, p5, p6, p7, p8, inr) \
     if ((inr) != 0xffffffffu) clt256v2_slow(p0, p1, p2, p3, p4, p5, p6, p7, p8, ~(inr), model, slow);
 
-// byte m of z = 6-bit bin of one sample; bin b of this thread's column is 128 bytes * b above hp
+// byte m of z = 6-bit bin of one sample; bin b of this thread's column is 128 bytes * b above hp.
+// CLT256V2_FMA_EXTRACT: the byte is isolated on the FMA pipe (z * 2^(24-8m), then the high word of
+// * 2^8, multipliers read from registers ptxas cannot fold) instead of one PRMT on the ALU pipe.
+#ifndef CLT256V2_FMA_EXTRACT
+#define CLT256V2_FMA_EXTRACT 0   /* measured: 459 vs 471 Gsamples/s -- the multiply-high chain costs more than the PRMT it saves */
+#endif
+#if CLT256V2_FMA_EXTRACT
+#define CLT256V2_RMW_LD(nm, z, m)                                                                         \
+    uint32_t a##nm, h##nm;                                                                                \
+    asm volatile("{\n\t.reg .b32 s, t;\n\tmul.lo.u32 s, %2, %4;\n\tmul.hi.u32 t, s, %5;\n\tmad.lo.u32 %0, t, 128, %3;\n\t" \
+                 "ld.shared.u32 %1, [%0];\n\t}"                                                           \
+                 : "=r"(a##nm), "=r"(h##nm) : "r"(z), "r"(hp), "r"(kshl[m]), "r"(k256));
+#else
 #define CLT256V2_RMW_LD(nm, z, m)                                                                        \
     uint32_t a##nm, h##nm;                                                                               \
     asm volatile("{\n\t.reg .b32 t;\n\tprmt.b32 t, %2, 0, 0x444" #m ";\n\tmad.lo.u32 %0, t, 128, %3;\n\t" \
                  "ld.shared.u32 %1, [%0];\n\t}"                                                          \
                  : "=r"(a##nm), "=r"(h##nm) : "r"(z), "r"(hp));
+#endif
 #define CLT256V2_RMW_ST(nm)                                                                              \
     asm volatile("{\n\t.reg .b32 t;\n\tmad.lo.u32 t, %1, %2, %2;\n\tst.shared.u32 [%0], t;\n\t}" ::"r"(a##nm), "r"(h##nm), "r"(one));
 
@@ -164,6 +177,19 @@ clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
     for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
     __syncthreads();
     const uint32_t hp = (uint32_t)__cvta_generic_to_shared(fast + (tid >> 5) * 2048 + (tid & 31));
+    const uint32_t k256 = one << 8;                                  // `one` is 1, unknown to the compiler
+    const uint32_t kshl[4] = {one << 24, one << 16, one << 8, one};
+    (void)k256; (void)kshl;
+    const uint32_t kshr1 = one << 31, kshr2 = one << 30, kshr4 = one << 28;   // x >> s == umulhi(x, 2^(32-s))
+#ifndef CLT256V2_FMA_SHR
+#define CLT256V2_FMA_SHR 1
+#endif
+#if CLT256V2_FMA_SHR
+#define CLT256V2_SHR(x, s) __umulhi((x), kshr##s)
+#else
+#define CLT256V2_SHR(x, s) ((x) >> (s))
+#endif
+    (void)kshr1; (void)kshr2; (void)kshr4;
 #define CLT256V2_SECTION_RESIDENT_DECL
 #include "clt256_v2_gen.inc"
 #undef CLT256V2_SECTION_RESIDENT_DECL

@@ -144,7 +144,8 @@ def tail_lines(shape, kind="hist"):
         nm = "q%d" % b
         em.emit("const uint32_t %s = %s & inr;" % (nm, src))
         q.append(nm)
-    gen_transpose(em, q, decl="const uint32_t ")
+    # right shifts as multiply-high by a power of two held in a register: FMA pipe instead of the ALU pipe
+    gen_transpose(em, q, decl="const uint32_t ", shr="CLT256V2_SHR(%s, %d)")
     return em.lines, em.ops
 
 
