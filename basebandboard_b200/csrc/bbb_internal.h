@@ -54,6 +54,7 @@ struct bbb_ctx {
     uint32_t tune_spec_min_steps = 512; // fewest clocks per stream worth a specialised launch
     uint32_t tune_spec_max_blocks = 0;  // 0: one CTA per SM
     uint64_t tune_slicer_chunk_bits = 0; // 0: 2^27 PRBS bits per pass of the slicer-loop composite
+    int tune_dec_full_stream = 0;       // 1: decimated samples by the full stream + pick (never clt256_dec_kernel)
     int nest = 0;                       // > 0 inside a composite ABI call (begin_call/end_call are the outer call's)
     uint32_t tune_prbs_chunk_words = 0; // 0: automatic detector chunk length (64-bit words)
     uint32_t tune_prbs_stream_reps = 0; // 0: automatic stream-kernel repetitions per warp
@@ -115,3 +116,6 @@ void bbb_prbs_free_tables(bbb_ctx *ctx);
 int bbb_clt_run_device(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
                        uint64_t *d_hist /*n+1 u64 or null*/, int8_t *d_out8, int16_t *d_out16,
                        uint32_t noise_var, uint32_t *d_out_words32);
+// d_out[j] = g[first + j*spb + delay], j < nd (int8, gateware widths)
+int bbb_clt_run_decimated(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t nd, uint32_t spb, uint32_t delay,
+                          int8_t *d_out);

@@ -259,6 +259,9 @@ int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c, int kind);
 int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model, const uint32_t *planes,
                         unsigned long long *hist);
 int bbb_clt_spec_stream_ok(const bbb_ctx *c, int kind);
+int bbb_clt_spec_dec_ok(const bbb_ctx *c);
+int bbb_clt_spec_dec_launch(bbb_ctx *c, uint32_t blocks, uint32_t Ld, uint32_t spb, uint32_t delay, const uint32_t *planes,
+                            int8_t *out);
 int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L, const uint32_t *planes, void *out,
                                uint32_t noise_var);
 
@@ -459,6 +462,85 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
     return BBB_OK;
 }
 
+// out[j] = in[j * spb + delay]
+__global__ void decimate_kernel(const int8_t *__restrict__ in, uint64_t nd, uint32_t spb, uint32_t delay, int8_t *__restrict__ out)
+{
+    for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < nd; j += (uint64_t)gridDim.x * blockDim.x)
+        out[j] = in[j * spb + delay];
+}
+
+// Decimated int8 samples, d_out[j] = g[first + j*spb + delay] for j < nd (gateware widths): the sample the
+// receiver keeps of each bit period (rx.py:18-19).  The shipped n256 matrix runs clt256_dec_kernel
+// (one CLT tree per spb clocks); anything else, and the ragged tail, generates the full stream into a
+// bounded scratch buffer and picks every spb-th byte.
+int bbb_clt_run_decimated(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t nd, uint32_t spb, uint32_t delay,
+                          int8_t *d_out)
+{
+    const uint32_t n = c->n, nw64 = (n + 63) / 64;
+    if (n & (n - 1)) return c->fail(BBB_EINVAL, "CLTGRNG needs n a power of two (rng.py:73-74), n=%u", n);
+    if (n > 256) return c->fail(BBB_EINVAL, "int8 samples need n <= 256");
+    if (!spb || delay >= spb) return c->fail(BBB_EINVAL, "delay < spb required");
+    if (spb == 1) return bbb_clt_run_device(c, x0, first, nd, BBB_MODEL_GATEWARE, nullptr, d_out, nullptr, 1, nullptr);
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    const bool spec = bbb_clt_spec_dec_ok(c) && !c->tune_dec_full_stream && ((uintptr_t)d_out & 31) == 0;
+    const uint64_t spbk = (uint64_t)bbb_clt_spec_streams_per_block(c, true);   // streams per CTA
+    uint64_t xl[BBB_MAX_NW64] = {0};
+    uint64_t done = 0;
+    if (spec) {
+        memcpy(xl, x0, nw64 * sizeof(uint64_t));
+        advance_state(c, xl, first);
+    }
+    while (done < nd) {
+        const uint64_t rem = nd - done;
+        if (spec && spbk && (done & 31) == 0) {
+            const uint64_t max_blocks = c->tune_spec_max_blocks ? c->tune_spec_max_blocks
+                                        : (uint64_t)c->sm_count * bbb_clt_spec_blocks_per_sm(c, 1);
+            uint64_t blocks = rem / (spbk * 32);
+            if (blocks > max_blocks) blocks = max_blocks;
+            uint64_t Ld = blocks ? rem / (blocks * spbk) : 0;
+            if (Ld > (1ull << 26)) Ld = 1ull << 26;
+            Ld &= ~31ull;                                   // 32 sampled clocks per flush (one full sector per stream)
+            if (blocks >= 1 && Ld >= 32) {
+                const uint64_t S = blocks * spbk, L = Ld * spb;
+                const uint32_t T = (uint32_t)(S / 32);
+                uint32_t nbits = 0;
+                while (nbits < 40 && ((S - 1) >> nbits)) nbits++;
+                uint32_t *dJ = upload_jump_ops(c, L, nbits);
+                if (!dJ) return BBB_ECUDA;
+                uint32_t *d_planes = (uint32_t *)c->scratch(1, (size_t)n * T * 4);
+                if (!d_planes) return BBB_ECUDA;
+                uint64_t x1[BBB_MAX_NW64];                  // the tree of a stream's state BEFORE each clock: start one clock in
+                memcpy(x1, xl, sizeof x1);
+                advance_state(c, x1, 1);
+                SeedStart xs;
+                to_seed(x1, nw64, xs);
+                int rc = launch_seed(c, dJ, xs, nbits, T, d_planes);
+                if (rc) return rc;
+                rc = bbb_clt_spec_dec_launch(c, (uint32_t)blocks, (uint32_t)Ld, spb, delay, d_planes, d_out + done);
+                if (rc) return rc;
+                advance_state(c, xl, S * L);
+                done += S * Ld;
+                continue;
+            }
+        }
+        // full stream of a bounded piece, then every spb-th byte
+        uint64_t piece = rem;
+        const uint64_t cap = (1ull << 28) / spb;
+        if (piece > cap) piece = cap;
+        int8_t *tmp = (int8_t *)c->scratch(13, (size_t)piece * spb);
+        if (!tmp) return BBB_ECUDA;
+        int rc = bbb_clt_run_device(c, x0, first + done * spb, piece * spb, BBB_MODEL_GATEWARE, nullptr, tmp, nullptr, 1, nullptr);
+        if (rc) return rc;
+        const uint64_t want = (piece + 255) / 256, cap_blocks = (uint64_t)c->sm_count * 16;
+        decimate_kernel<<<(uint32_t)(want < cap_blocks ? want : cap_blocks), 256, 0, c->stream>>>(tmp, piece, spb, delay, d_out + done);
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        if (spec) advance_state(c, xl, piece * spb);
+        done += piece;
+    }
+    return BBB_OK;
+}
+
 // ---------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------
@@ -548,6 +630,36 @@ int bbb_clt_stream(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t coun
                             out16 ? (int16_t *)d : nullptr);
     if (rc) return rc;
     BBB_CUDA(c, c->d2h(out8 ? (void *)out8 : (void *)out16, d, bytes));
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return BBB_OK;
+}
+
+int bbb_clt_stream_dec_dev(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t spb, uint32_t delay,
+                           int8_t *out8_dev)
+{
+    int rc = check_loaded(c, x0);
+    if (rc) return rc;
+    if (!out8_dev) return c->fail(BBB_EINVAL, "out is null");
+    if (!spb || spb > 64 || delay >= spb) return c->fail(BBB_EINVAL, "1 <= spb <= 64 and delay < spb (rx.py:18-19)");
+    if ((first + count * spb) >> 62) return c->fail(BBB_EINVAL, "sample range too large");
+    c->begin_call();
+    rc = bbb_clt_run_decimated(c, x0, first, count, spb, delay, out8_dev);
+    if (rc) return rc;
+    c->end_call();
+    return BBB_OK;
+}
+
+int bbb_clt_stream_dec(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t spb, uint32_t delay,
+                       int8_t *out8)
+{
+    int rc = check_loaded(c, x0);
+    if (rc) return rc;
+    if (!out8) return c->fail(BBB_EINVAL, "out is null");
+    void *d = c->scratch(4, count ? (size_t)count : 1);
+    if (!d) return BBB_ECUDA;
+    rc = bbb_clt_stream_dec_dev(c, x0, first, count, spb, delay, (int8_t *)d);
+    if (rc) return rc;
+    BBB_CUDA(c, c->d2h(out8, d, (size_t)count));
     BBB_CUDA(c, cudaStreamSynchronize(c->stream));
     return BBB_OK;
 }

@@ -454,6 +454,71 @@ clt256_s8v2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, 
     }
 }
 
+// Decimated sample stream: out[j] = g[j * spb + delay] of every stream -- what the receiver keeps of the
+// noise (rx.py:18-19 takes sample `delay` of the spb samples of a bit).  The recurrence has to be clocked
+// through all spb samples, but only the sampled clock needs the CLT tree: that clock is the "s8" body
+// (popcount network, un-slice, slab), the other spb-1 are the clock alone ("plain" body: 492 LOP3, the
+// loads and stores of the non-resident planes).  Ld = decimated samples per stream (a multiple of 32).
+__global__ void __launch_bounds__(CLT256V2_B, CLT256V2_CTAS_PER_SM)
+clt256_dec_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t Ld, uint32_t spb, uint32_t delay,
+                  int8_t *__restrict__ out, uint32_t *__restrict__ slab_base)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+    uint32_t *const st = (uint32_t *)smem4 + tid;
+    for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+    uint32_t *const slab = slab_base + t;
+    int8_t *const outp = out + (size_t)t * 32u * Ld;          // stream j: decimated sample offset j*Ld
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < Ld; it++) {
+#pragma unroll 1
+        for (uint32_t ph = 0; ph < spb; ph++) {
+            if (ph == delay) {
+#define CLT256V2_SECTION_S8_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_S8_BODY
+            } else {
+#define CLT256V2_SECTION_P_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_P_BODY
+            }
+        }
+        if ((it & (CLT256V2_S8_K - 1u)) == 0u && it != 0u)
+            clt256v2_s8_flush(slab, T, outp, it - CLT256V2_S8_K, Ld, false, 0);
+    }
+    {
+        const uint32_t it = Ld;      // the last sampled clock's tail (Ld is a multiple of 32: slab row 31)
+#define CLT256V2_SECTION_S8_TAIL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_S8_TAIL
+        clt256v2_s8_flush(slab, T, outp, Ld - CLT256V2_S8_K, Ld, false, 0);
+    }
+}
+
+int bbb_clt_spec_dec_ok(const bbb_ctx *c)
+{
+    return c->shipped == 256 && !c->tune_no_spec && c->tune_spec_variant != 1;
+}
+
+int bbb_clt_spec_dec_launch(bbb_ctx *c, uint32_t blocks, uint32_t Ld, uint32_t spb, uint32_t delay, const uint32_t *planes,
+                            int8_t *out)
+{
+    const uint32_t T = blocks * CLT256V2_B;
+    uint32_t *slab = (uint32_t *)c->scratch(11, (size_t)CLT256V2_S8_K * 8 * T * 4);
+    if (!slab) return BBB_ECUDA;
+    BBB_CUDA(c, cudaFuncSetAttribute(clt256_dec_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2_STATE_BYTES));
+    clt256_dec_kernel<<<blocks, CLT256V2_B, CLT256V2_STATE_BYTES, c->stream>>>(planes, T, Ld, spb, delay, out, slab);
+    c->last_kernel = "clt256_dec";
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    return BBB_OK;
+}
+
 // raw URNG words (LUTOPT.x after every clock, rng.py:27): 32 x 32 bit transposes of the new planes,
 // four 32-bit words of a stream leave as one 128-bit store (a stream's clock = one 32-byte sector)
 #define CLT256W_SECTION_PERM

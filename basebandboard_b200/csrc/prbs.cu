@@ -663,6 +663,22 @@ slicer_err_kernel(const int8_t *__restrict__ g, const uint64_t *__restrict__ tx,
     const uint64_t w = tx[j];
     const int8_t *gp = g + (j * 64) * spb + delay;
     uint64_t rx = 0;
+    if (spb == 1 && ((uintptr_t)g & 15) == 0) {          // decimated noise: 64 consecutive bytes, four 128-bit loads
+#pragma unroll
+        for (uint32_t q = 0; q < 4; q++) {
+            const uint4 v = __ldcs((const uint4 *)gp + q);
+            const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (uint32_t i = 0; i < 16; i++) {
+                const int32_t noise = (int32_t)(int8_t)((vv[i >> 2] >> (8 * (i & 3))) & 0xffu) * noise_var;
+                const int32_t x = (((w >> (16 * q + i)) & 1ull) ? amp : -amp) + noise;
+                const int32_t x12 = ((x + 2048) & 4095) - 2048;
+                rx |= (uint64_t)(x12 >= 0) << (16 * q + i);
+            }
+        }
+        err[j] = rx ^ w;
+        return;
+    }
 #pragma unroll 4
     for (uint32_t i = 0; i < 64; i++) {
         const int32_t noise = (int32_t)gp[(size_t)i * spb] * noise_var;
@@ -707,19 +723,20 @@ int bbb_prbs_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t 
     else { d0.bit_in = 0; d0.prbs = 1; d0.err_sr = (uint32_t)((1ull << k) - 1); d0.reload_ctr = 0; }
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
-    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 29);   // 4 GiB of int8 samples per pass
+    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 32);   // 4 GiB of sampled int8 noise per pass
     uint32_t rounds = 0;
     for (uint64_t off = 0; off < nbits; off += CH) {
         const uint64_t nb = nbits - off < CH ? nbits - off : CH, nw = nb / 64;
-        int8_t *d_g = (int8_t *)c->scratch(9, (size_t)nb * spb);
+        int8_t *d_g = (int8_t *)c->scratch(9, (size_t)nb);
         uint64_t *d_tx = (uint64_t *)c->scratch(10, (size_t)nw * 16);
         if (!d_g || !d_tx) return BBB_ECUDA;
         uint64_t *d_err = d_tx + nw;
         rc = bbb_prbs_stream_dev(c, k, 1u, first_bit + off, nb, d_tx);
         if (rc) return rc;
-        rc = bbb_clt_stream_dev(c, x0, (first_bit + off) * spb, nb * spb, BBB_MODEL_GATEWARE, 1u, d_g, nullptr);
+        // only the sample the receiver keeps of each bit (rx.py:18-19) is materialised: 1 byte per bit
+        rc = bbb_clt_run_decimated(c, x0, (first_bit + off) * spb, nb, spb, delay, d_g);
         if (rc) return rc;
-        slicer_err_kernel<<<(uint32_t)((nw + 255) / 256), 256, 0, c->stream>>>(d_g, d_tx, nw, spb, delay, (int32_t)amplitude,
+        slicer_err_kernel<<<(uint32_t)((nw + 255) / 256), 256, 0, c->stream>>>(d_g, d_tx, nw, 1u, 0u, (int32_t)amplitude,
                                                                                 (int32_t)noise_var, d_err);
         c->last_launches++;
         BBB_CUDA(c, cudaGetLastError());
@@ -859,7 +876,7 @@ shaped_slicer_err_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64
             const int32_t c = cf.c[k];
             a += ((win >> q) & 1u) ? c : -c;
         }
-        const int32_t x = a + (int32_t)g[r * 8 + delay] * noise_var;
+        const int32_t x = a + (int32_t)g[r] * noise_var;          // g: the sampled phase only, one byte per bit
         const int32_t x12 = ((x + 2048) & 4095) - 2048;
         const uint32_t b = (win >> 4) & 1u;                    // b[J-4] = the bit being decided
         e |= (uint64_t)((uint32_t)(x12 >= 0) ^ b) << i;
@@ -972,7 +989,7 @@ int bbb_prbs_shaped_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, ui
     else { d0.bit_in = 0; d0.prbs = 1; d0.err_sr = (uint32_t)((1ull << k) - 1); d0.reload_ctr = 0; }
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
-    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 29);   // 4 GiB of int8 samples per pass
+    const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 32);   // 4 GiB of sampled int8 noise per pass
     uint32_t rounds = 0;
     for (uint64_t off = 0; off < nbits; off += CH) {
         const uint64_t nb = nbits - off < CH ? nbits - off : CH, nw = nb / 64;
@@ -982,10 +999,10 @@ int bbb_prbs_shaped_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, ui
         if (rc) return rc;
         const uint64_t span_words = (((first_bit + off) - (uint64_t)origin) + nb + 64 + 63) / 64;
         uint64_t *d_err = d_tx + span_words;
-        int8_t *d_g = (int8_t *)c->scratch(9, (size_t)nb * 8);
+        int8_t *d_g = (int8_t *)c->scratch(9, (size_t)nb);
         if (!d_g) return BBB_ECUDA;
-        // the sample of bit J is 8*(J+4)+delay
-        rc = bbb_clt_stream_dev(c, x0, (first_bit + off + 4) * 8, nb * 8, BBB_MODEL_GATEWARE, 1u, d_g, nullptr);
+        // the sample of bit J is 8*(J+4)+delay: only that one of the 8 noise samples is materialised
+        rc = bbb_clt_run_decimated(c, x0, (first_bit + off + 4) * 8, nb, 8u, delay, d_g);
         if (rc) return rc;
         shaped_slicer_err_kernel<<<(uint32_t)((nw + 255) / 256), 256, 0, c->stream>>>(
             d_tx, origin, (int64_t)(first_bit + off), nw, cf, delay, d_g, (int32_t)noise_var, d_err);

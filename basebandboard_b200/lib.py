@@ -71,6 +71,8 @@ SIGNATURES = {
                                  _P(C.c_int8), _P(C.c_int16)]),
     "bbb_clt_stream_dev": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32,
                                      C.c_void_p, C.c_void_p]),
+    "bbb_clt_stream_dec": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, _P(C.c_int8)]),
+    "bbb_clt_stream_dec_dev": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]),
     "bbb_clt_stats": (C.c_int, [C.c_uint32, C.c_uint32, _u64p, _P(C.c_double)]),
     "bbb_prbs_tap": (C.c_uint32, [C.c_uint32]),
     "bbb_prbs_stream": (C.c_int, [_ctx, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, _u64p]),
@@ -281,6 +283,19 @@ class Context:
         p16 = C.c_void_p(dev_ptr) if elem_bytes == 2 else None
         self._check(self._L.bbb_clt_stream_dev(self._h, _ptr(x0, C.c_uint64), first, count, model,
                                                noise_var, p8, p16))
+
+    def clt_stream_dec(self, init, first, count, spb, delay):
+        """out[j] = g[first + j*spb + delay]: the sample of each bit period the receiver keeps (rx.py:18-19)."""
+        x0 = state_words(init, self.n)
+        out = np.zeros(count, dtype=np.int8)
+        self._check(self._L.bbb_clt_stream_dec(self._h, _ptr(x0, C.c_uint64), first, count, spb, delay,
+                                               _ptr(out, C.c_int8)))
+        return out
+
+    def clt_stream_dec_dev(self, init, first, count, spb, delay, dev_ptr):
+        x0 = state_words(init, self.n)
+        self._check(self._L.bbb_clt_stream_dec_dev(self._h, _ptr(x0, C.c_uint64), first, count, spb, delay,
+                                                   C.c_void_p(dev_ptr)))
 
     # ---- PRBS ------------------------------------------------------------------------------
     def prbs_stream(self, k, nbits, state0=1, first_bit=0):

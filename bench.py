@@ -224,7 +224,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
                     "2^%d bits per GPU (SURVEY 8f-1; replicas, not shards)" % (args.k, args.amplitude, args.noise_var,
                                                                             args.spb, args.log2_bits))
         dtype = "u32 GF(2) + int8/int32"
-        l2 = "intermediate sample buffer (%d MiB per pass) exceeds L2" % ((min(nbits, 1 << 27) * args.spb) >> 20)
+        l2 = "intermediate buffer = the one kept noise sample per bit (%d MiB per pass) exceeds L2" % (min(nbits, 1 << 32) >> 20)
     elif w == "tx_stream":
         from basebandboard_b200 import shaper
         nbits = 1 << (args.log2_bits - 7)                 # 16 B per bit: 2^36 "bits" of budget = 8 GiB of TX words

@@ -129,6 +129,14 @@ int bbb_clt_stream(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t co
                    uint32_t noise_var, int8_t *out8, int16_t *out16);
 int bbb_clt_stream_dev(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
                        uint32_t noise_var, int8_t *out8_dev, int16_t *out16_dev);
+/* Decimated samples: out8[j] = g[first + j*spb + delay], j < count -- the one noise sample
+ * of each bit period the receiver keeps (gateware/bbb/rx.py:18-19: sample `delay` of the
+ * spb samples of a bit; noise from tx.py:69-76).  Gateware widths.  The generator is
+ * clocked through every sample; the CLT tree runs on the kept ones only. */
+int bbb_clt_stream_dec(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t spb,
+                       uint32_t delay, int8_t *out8);
+int bbb_clt_stream_dec_dev(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t spb,
+                           uint32_t delay, int8_t *out8_dev);
 /* clt-grng-evaluate.py:18-21 from an integer histogram, in f64 with a fixed
  * summation order: stats[0]=mean, [1]=variance (ddof=0), [2]=excess kurtosis,
  * [3]=chi-square against N(0, n/4) bin probabilities, [4]=chi-square against the

@@ -24,3 +24,12 @@ def orc():
     from oracle import oracle
     oracle.lib()
     return oracle
+
+
+def pytest_collection_finish(session):
+    """GPU sessions import torch before the first test touches libbbb_b200.so: on a fresh box the first
+    `import torch` pages in gigabytes of libraries, and doing that from the middle of a test, with the CUDA
+    context of the C ABI already live, once ended in SIGABRT inside the import (gpurun_out/s22, not
+    reproducible on the next three runs).  Importing it up front keeps that on the well-trodden path."""
+    if any(item.get_closest_marker("gpu") for item in session.items):
+        import torch  # noqa: F401

@@ -6,7 +6,7 @@ models by tests/test_oracle_gen.py."""
 import numpy as np
 import pytest
 
-from basebandboard_b200 import recurrences
+from basebandboard_b200 import lib, recurrences
 
 pytestmark = pytest.mark.gpu
 
@@ -217,6 +217,59 @@ def test_spec256_int8_stream_matches_oracle(ctx, orc, blocks, min_steps, count, 
         ctx.set_tuning("clt_spec_min_steps", 512)
         ctx.set_tuning("clt_spec_max_blocks", 0)
         ctx.set_tuning("clt_spec_variant", 2)
+
+
+# ---- decimated sample stream (clt256_dec: the CLT tree on every spb-th clock only) ------------------
+@pytest.mark.parametrize("spb,delay,blocks,count,first", [(8, 0, 1, 4096 * 40 + 77, 0), (8, 5, 2, 2 * 4096 * 70 + 13, (1 << 33) + 5),
+                                                          (4, 3, 1, 4096 * 33, 64), (2, 1, 3, 3 * 4096 * 100 + 5, (1 << 40) + 32),
+                                                          (16, 15, 1, 4096 * 32 + 1, 7), (3, 2, 1, 4096 * 64 + 9, 1),
+                                                          (8, 7, 1, 1000, 12345), (1, 0, 1, 4096 * 40 + 3, 99)])
+def test_decimated_stream_matches_oracle(ctx, orc, spb, delay, blocks, count, first):
+    """out[j] = g[first + j*spb + delay] (the sample of a bit period the receiver keeps, rx.py:18-19):
+    clt256_dec_kernel + ragged tail == every spb-th sample of the oracle's full stream; and the
+    full-stream-then-pick path (tuning knob) gives the same bytes."""
+    ctx.lutopt_load_shipped(256)
+    ctx.set_tuning("clt_spec_max_blocks", blocks)
+    try:
+        got = ctx.clt_stream_dec(1, first, count, spb, delay)
+        if spb > 1 and count >= 4096 * 32:
+            assert ctx.last_kernel in ("clt256_dec", "generic", "clt256_s8v2") and ctx.last_launches >= 2
+        full = orc.clt_run(recurrences.packed(256), 1, first, count * spb, model=0, want=("out8",))["out8"]
+        assert np.array_equal(got, full[delay::spb])
+        ctx.set_tuning("dec_full_stream", 1)
+        assert np.array_equal(ctx.clt_stream_dec(1, first, count, spb, delay), got)
+    finally:
+        ctx.set_tuning("dec_full_stream", 0)
+        ctx.set_tuning("clt_spec_max_blocks", 0)
+    with pytest.raises(lib.BBBError):
+        ctx.clt_stream_dec(1, 0, 64, 8, 8)               # delay must be < spb
+    with pytest.raises(lib.BBBError):
+        ctx.clt_stream_dec(1, 0, 64, 0, 0)
+
+
+def test_decimated_stream_other_matrices(ctx, orc):
+    """A recurrence without a straight-line kernel takes the full stream + pick path."""
+    for n in (32, 64):
+        ctx.lutopt_load_shipped(n)
+        got = ctx.clt_stream_dec(1, 1000, 5000, 8, 3)
+        full = orc.clt_run(recurrences.packed(n), 1, 1000, 5000 * 8, model=0, want=("out8",))["out8"]
+        assert np.array_equal(got, full[3::8])
+    ctx.lutopt_load_shipped(256)
+
+
+def test_decimated_stream_equals_full_stream_large(ctx):
+    """Full geometry (296 CTAs, several launches + tail): clt256_dec == every 8th byte of clt256_s8v2."""
+    import torch
+    ctx.lutopt_load_shipped(256)
+    nd = 296 * 4096 * 64 + 4096 * 35 + 11
+    a = torch.empty(nd, dtype=torch.int8, device="cuda")
+    b = torch.empty(nd * 8, dtype=torch.int8, device="cuda")
+    ctx.clt_stream_dec_dev(1, 1 << 36, nd, 8, 6, a.data_ptr())
+    ctx.sync()
+    assert ctx.last_launches >= 4
+    ctx.clt_stream_dev(1, 1 << 36, nd * 8, 0, 1, b.data_ptr(), 1)
+    ctx.sync()
+    assert bool(torch.equal(a, b[6::8]))
 
 
 @pytest.mark.parametrize("variant", [1, 2])

@@ -209,6 +209,25 @@ def test_detect_with_supplied_error_words(ctx, orc, k):
     assert want["reload_events"] >= 2 and want["err_valid"] > 100
 
 
+def test_slicer_loop_sampled_noise_equals_full_stream_large(ctx):
+    """Full geometry: the loop over the decimated noise stream (clt256_dec, 1 byte per bit) gives the counters
+    and detector state of the loop over the full 8-samples-per-bit stream (tuning knob dec_full_stream)."""
+    from basebandboard_b200 import lib
+    ctx.lutopt_load_shipped(256)
+    k, nbits, first = 31, (1 << 26) + 64 * 777, 64 * 5 + 3
+    res = []
+    for full in (0, 1):
+        ctx.set_tuning("dec_full_stream", full)
+        try:
+            det = lib.DetState(0, 1, (1 << k) - 1, 0)
+            got = ctx.prbs_slicer_detect(k, nbits, init=1, amplitude=256, noise_var=12, spb=8, delay=3, first_bit=first, det=det)
+            res.append((got, (det.bit_in, det.prbs, det.err_sr, det.reload_ctr)))
+        finally:
+            ctx.set_tuning("dec_full_stream", 0)
+    assert res[0] == res[1]
+    assert res[0][0]["injected"] > 100000
+
+
 @pytest.mark.parametrize("k,amp,nv,spb,delay", [(7, 300, 8, 8, 0), (15, 200, 15, 8, 5), (31, 900, 15, 4, 3),
                                                 (23, 64, 1, 1, 0), (9, 2047, 15, 2, 1)])
 def test_slicer_loop_matches_oracle(ctx, orc, k, amp, nv, spb, delay):

@@ -175,7 +175,7 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
         for b in rows[r]:
             taps_at[pos[b]].append(r)
     hooks = rmw_hooks_v2() if kind == "hist" else {}
-    tail, tail_ops = tail_lines(shape, kind) if (shape is not None and kind != "words") else ([], {})
+    tail, tail_ops = tail_lines(shape, kind) if (shape is not None and kind not in ("words", "plain")) else ([], {})
     per_step = -(-len(tail) // TAIL_STEPS) if tail else 0
     heap = BitHeap(em)
     pending = {r: [] for r in range(N)}       # raw planes not yet folded
@@ -219,7 +219,7 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
         for ln in hooks.get(t, []):
             em.emit(ln)
         w = wexpr(t)
-        if kind != "words":
+        if kind not in ("words", "plain"):
             heap.add(w, parity(perm[t]) == 1)
             heap.reduce()
         for r in taps_at[t]:
@@ -246,6 +246,9 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
     assert not store_at, store_at
     assert not tail
     assert assigned == set(resident)
+    if kind == "plain":
+        # the clock alone (no popcount network, nothing emitted): the clocks between two sampled ones
+        return em, perm
     if kind == "words":
         # raw URNG words: the state AFTER the clock, un-sliced 32 planes at a time (resident planes from
         # their registers, the others from their slots, where the clock has just stored them)
@@ -279,6 +282,7 @@ def main():
     em8, _ = body_hist_v2(rows, pos, resident, shape, "s8")
     emw, _ = body_hist_v2(rows, pos, resident, shape, "words")
     tail8, _ = tail_lines(shape, "s8")
+    emp, _ = body_hist_v2(rows, pos, resident, shape, "plain")
     out = os.path.join(ROOT, "basebandboard_b200", "csrc", "clt256_v2_gen.inc")
     with open(out, "w") as f:
         f.write("// GENERATED by tools/gen_clt256_v2.py -- do not edit.  One-pass LUTOPT(n256) clock + CLTGRNG popcount\n")
@@ -305,6 +309,8 @@ def main():
         f.write("\n".join(tail8))
         f.write("\n#endif\n#ifdef CLT256V2_SECTION_W_BODY\n// same clock without the popcount network, then the new state as raw URNG words (rng.py:27)\n")
         f.write("\n".join(emw.lines))
+        f.write("\n#endif\n#ifdef CLT256V2_SECTION_P_BODY\n// the clock alone: no popcount network, nothing emitted (decimated sample streams)\n")
+        f.write("\n".join(emp.lines))
         f.write("\n#endif\n")
     print("wrote", out, "ops", em.ops, "peak live", peak, "resident", len(resident), file=sys.stderr)
 
