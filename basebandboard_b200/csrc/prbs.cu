@@ -795,15 +795,59 @@ __device__ __forceinline__ void shaped8(const ShaperCoef &cf, uint32_t win, int3
 // thread per bit period: eight int16 = one 128-bit streaming store.  g may be null (noise off).
 // The eight sums of a bit period depend on 8 of the 9 window bits each (phases 0..3 on b[J-8..J-1],
 // phases 4..7 on b[J-7..J]), so a CTA first tabulates them: T2[pp][idx] = the sums of phases 2pp and
-// 2pp+1 as a packed int16 pair for every 8-bit pattern (4 KB of shared memory, 8 adds per entry).  A
-// bit period is then 4 LDS.32 and one store: the kernel is bound by HBM writes, not by the ALU.
-__global__ void __launch_bounds__(256)
+// 2pp+1 as a packed int16 pair for every 8-bit pattern (8 adds per entry).  A bit period is then 4 LDS.32
+// and one store: the kernel is bound by HBM writes, not by the ALU.
+#ifndef SHAPER_COPIES
+#define SHAPER_COPIES 32                 /* table copies (a power of two <= 32): lane l reads copy l % SHAPER_COPIES */
+#endif
+#ifndef SHAPER_CTAS
+#define SHAPER_CTAS 1
+#endif
+#ifndef SHAPER_UNROLL
+#define SHAPER_UNROLL 4
+#endif
+#ifndef SHAPER_INTERLEAVE
+#define SHAPER_INTERLEAVE 1
+#endif
+#define SHAPER_THREADS 1024
+constexpr int kShaperUnroll = SHAPER_UNROLL;
+#define SHAPER_TBYTES (256 * SHAPER_COPIES * 4)      /* one phase-pair table */
+#define SHAPER_SMEM (4 * SHAPER_TBYTES)
+#define SHAPER_LOG2C (SHAPER_COPIES == 32 ? 5 : SHAPER_COPIES == 16 ? 4 : SHAPER_COPIES == 8 ? 3 : SHAPER_COPIES == 4 ? 2 : SHAPER_COPIES == 2 ? 1 : 0)
+
+// one bit period: table words of the lane's copy (byte offsets), noise add and 12-bit wrap when asked, one 128-bit store
+__device__ __forceinline__ void shaper_emit(const char *Tl, uint32_t win, uint64_t r, uint32_t bit_en,
+                                            const int8_t *__restrict__ g, int32_t noise_var, uint4 *__restrict__ out)
+{
+    const uint32_t lo = (win & 255u) << (SHAPER_LOG2C + 2), hi = (win >> 1) << (SHAPER_LOG2C + 2);
+    uint32_t o[4] = {*(const uint32_t *)(Tl + lo), *(const uint32_t *)(Tl + SHAPER_TBYTES + lo),
+                     *(const uint32_t *)(Tl + 2 * SHAPER_TBYTES + hi), *(const uint32_t *)(Tl + 3 * SHAPER_TBYTES + hi)};
+    if (g || !bit_en) {
+        uint2 gg = make_uint2(0u, 0u);
+        if (g) gg = *(const uint2 *)(g + r * 8);
+#pragma unroll
+        for (int p = 0; p < 8; p++) {
+            const int32_t sp = bit_en ? (int32_t)(int16_t)(o[p >> 1] >> (16 * (p & 1))) : 0;
+            const int32_t nz = (int32_t)(int8_t)(((p < 4 ? gg.x : gg.y) >> (8 * (p & 3))) & 0xffu) * noise_var;
+            const int32_t x = sp + nz;
+            const uint32_t x12 = (uint32_t)((((x + 2048) & 4095) - 2048)) & 0xffffu;
+            o[p >> 1] = (p & 1) ? (o[p >> 1] & 0xffffu) | (x12 << 16) : (o[p >> 1] & 0xffff0000u) | x12;
+        }
+    }
+    __stcs(out + r, make_uint4(o[0], o[1], o[2], o[3]));
+}
+
+// Table layout: one private copy per lane, word (pp * 256 + idx) * 32 + lane (128 KB): the four lookups of
+// a bit period are conflict-free whatever the data (a single 4 KB table costs ~3.5 wavefronts per lookup
+// on random patterns, which made shared memory, not HBM, the limit: 4.6 TB/s).  One 1024-thread CTA per SM.
+__global__ void __launch_bounds__(SHAPER_THREADS, SHAPER_CTAS)
 shaper_stream_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t first_bit, uint64_t nbits, ShaperCoef cf,
                      uint32_t bit_en, const int8_t *__restrict__ g, int32_t noise_var, uint4 *__restrict__ out)
 {
-    __shared__ uint32_t T2[4][256];
-    for (uint32_t e = threadIdx.x; e < 1024; e += blockDim.x) {
-        const uint32_t pp = e >> 8, idx = e & 255u;
+    extern __shared__ uint32_t T2[];
+    __shared__ uint32_t stage[1024];
+    {
+        const uint32_t e = threadIdx.x, pp = e >> 8, idx = e & 255u;
         uint32_t pair = 0;
 #pragma unroll
         for (int h = 0; h < 2; h++) {
@@ -818,39 +862,77 @@ shaper_stream_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t f
             }
             pair |= ((uint32_t)a & 0xffffu) << (16 * h);
         }
-        T2[pp][idx] = pair;
+        stage[e] = pair;
     }
     __syncthreads();
-    // grid-stride over bit periods: the table is built once per CTA, stores stay coalesced
-    for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < nbits; r += (uint64_t)gridDim.x * blockDim.x) {
-        const int64_t J = first_bit + (int64_t)r;
-        uint32_t win = 0;                         // bit q = b[J-8+q]
-        if (J >= 8) {
-            const uint64_t a = (uint64_t)(J - 8 - origin);
-            const uint32_t sh = (uint32_t)(a & 63);
-            uint64_t w = txw[a >> 6] >> sh;
-            if (sh > 55) w |= txw[(a >> 6) + 1] << (64 - sh);
-            win = (uint32_t)w & 0x1ffu;
-        } else {
+    for (uint32_t i = threadIdx.x; i < 4 * 256 * SHAPER_COPIES; i += SHAPER_THREADS) T2[i] = stage[i >> SHAPER_LOG2C];
+    __syncthreads();
+    // A warp owns a contiguous run of 32-period steps; lane l takes period R + l of each step, so a step is one
+    // coalesced 512-byte store.  The 9-bit window of lane l starts at stream bit c0 + R + l: with R a multiple of
+    // 32 the shift is a per-lane constant and the window is one funnel shift of two consecutive 32-bit words of
+    // the packed PRBS stream, both L1 hits.
+    const uint32_t lane = threadIdx.x & 31u;
+    const char *const Tl = (const char *)(T2 + (lane & (SHAPER_COPIES - 1u)));
+    const uint32_t *const t32 = (const uint32_t *)txw;
+    const uint64_t nsteps = (nbits + 31) / 32;
+    // this warp's steps: s0, s0 + SS, ... < s1.  SHAPER_INTERLEAVE: a CTA owns a contiguous run and its 32 warps
+    // interleave (the CTA writes 16 KB contiguous per round: 148 write streams); else every warp owns its own run
+    constexpr uint64_t SS = SHAPER_INTERLEAVE ? SHAPER_THREADS / 32 : 1;
+    uint64_t s0, s1;
+    if (SHAPER_INTERLEAVE) {
+        const uint64_t per = (nsteps + gridDim.x - 1) / gridDim.x;
+        s0 = (uint64_t)blockIdx.x * per;
+        s1 = s0 + per;
+        s0 += threadIdx.x >> 5;
+    } else {
+        const uint64_t nwarps = (uint64_t)gridDim.x * (SHAPER_THREADS / 32);
+        const uint64_t per = (nsteps + nwarps - 1) / nwarps;
+        s0 = ((uint64_t)blockIdx.x * (SHAPER_THREADS / 32) + (threadIdx.x >> 5)) * per;
+        s1 = s0 + per;
+    }
+    if (s1 > nsteps) s1 = nsteps;
+    if (s0 >= s1) return;
+    if (first_bit < 8 && s0 == 0) {               // the start of time (b[m] = 0 for m < 0): bit by bit
+        const uint64_t r = lane;
+        if (r < nbits) {
+            const int64_t J = first_bit + (int64_t)r;
+            uint32_t win = 0;
 #pragma unroll
             for (int q = 0; q < 9; q++) win |= tx_bit(txw, J - 8 + q, origin) << q;
+            shaper_emit(Tl, win, r, bit_en, g, noise_var, out);
         }
-        const uint32_t lo = win & 255u, hi = win >> 1;
-        uint32_t o[4] = {T2[0][lo], T2[1][lo], T2[2][hi], T2[3][hi]};
-        if (g || !bit_en) {
-            uint2 gg = make_uint2(0u, 0u);
-            if (g) gg = *(const uint2 *)(g + r * 8);
-#pragma unroll
-            for (int p = 0; p < 8; p++) {
-                const int32_t sp = bit_en ? (int32_t)(int16_t)(o[p >> 1] >> (16 * (p & 1))) : 0;
-                const int32_t nz = (int32_t)(int8_t)(((p < 4 ? gg.x : gg.y) >> (8 * (p & 3))) & 0xffu) * noise_var;
-                const int32_t x = sp + nz;
-                const uint32_t x12 = (uint32_t)((((x + 2048) & 4095) - 2048)) & 0xffffu;
-                o[p >> 1] = (p & 1) ? (o[p >> 1] & 0xffffu) | (x12 << 16) : (o[p >> 1] & 0xffff0000u) | x12;
-            }
-        }
-        __stcs(out + r, make_uint4(o[0], o[1], o[2], o[3]));
+        s0 += SS;
+        if (s0 >= s1) return;
     }
+    const uint64_t a0 = (uint64_t)(first_bit - 8 - origin) + s0 * 32 + lane;   // first window bit of this lane
+    const uint32_t sh = (uint32_t)(a0 & 31);
+    const uint32_t *wp = t32 + (a0 >> 5);
+    uint64_t r = s0 * 32 + lane;
+    const uint64_t sf = s1 < nbits / 32 ? s1 : nbits / 32;      // steps below sf have all 32 lanes in range
+    uint64_t st = s0;
+    if (!g && bit_en) {
+        uint4 *op = out + r;
+#pragma unroll kShaperUnroll
+        for (; st < sf; st += SS) {
+            const uint32_t win = __funnelshift_r(wp[0], wp[1], sh);
+            wp += SS;
+            // byte offsets of the lane's table words
+            const uint32_t lo = (win & 255u) << (SHAPER_LOG2C + 2), hi = ((win >> 1) & 255u) << (SHAPER_LOG2C + 2);
+            __stcs(op, make_uint4(*(const uint32_t *)(Tl + lo), *(const uint32_t *)(Tl + SHAPER_TBYTES + lo),
+                                  *(const uint32_t *)(Tl + 2 * SHAPER_TBYTES + hi), *(const uint32_t *)(Tl + 3 * SHAPER_TBYTES + hi)));
+            op += 32 * SS;
+        }
+        r = st * 32 + lane;
+    } else {
+        for (; st < sf; st += SS) {
+            const uint32_t win = __funnelshift_r(wp[0], wp[1], sh) & 0x1ffu;
+            wp += SS;
+            shaper_emit(Tl, win, r, bit_en, g, noise_var, out);
+            r += 32 * SS;
+        }
+    }
+    if (st < s1 && r < nbits)                     // the ragged last step of the range
+        shaper_emit(Tl, __funnelshift_r(wp[0], wp[1], sh) & 0x1ffu, r, bit_en, g, noise_var, out);
 }
 
 // RX decisions through the shaped channel: bit J is decided on the sample 8*(J+4)+delay (the pulse of
@@ -891,7 +973,7 @@ static int shaper_tx_words(bbb_ctx *c, uint32_t k, uint64_t first, uint64_t nbit
 {
     const uint64_t org = first >= 64 ? first - 64 : 0;
     const uint64_t span = ((first - org) + nbits_with_lookahead + 63) & ~63ull;
-    uint64_t *d = (uint64_t *)c->scratch(10, (size_t)(span / 64 + extra_words) * 8);
+    uint64_t *d = (uint64_t *)c->scratch(10, (size_t)(span / 64 + extra_words + 1) * 8);   // + the word a window load may touch
     if (!d) return BBB_ECUDA;
     int rc = bbb_prbs_stream_dev(c, k, 1u, org, span, d);
     if (rc) return rc;
@@ -942,8 +1024,9 @@ int bbb_tx_stream_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits
             rc = bbb_clt_stream_dev(c, x0, (first_bit + off) * 8, nb * 8, BBB_MODEL_GATEWARE, 1u, d_g, nullptr);
             if (rc) return rc;
         }
-        const uint64_t want_blocks = (nb + 255) / 256, max_blocks = (uint64_t)c->sm_count * 16;
-        shaper_stream_kernel<<<(uint32_t)(want_blocks < max_blocks ? want_blocks : max_blocks), 256, 0, c->stream>>>(
+        const uint64_t want_blocks = (nb + SHAPER_THREADS - 1) / SHAPER_THREADS, max_blocks = (uint64_t)c->sm_count * SHAPER_CTAS;
+        BBB_CUDA(c, cudaFuncSetAttribute(shaper_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SHAPER_SMEM));
+        shaper_stream_kernel<<<(uint32_t)(want_blocks < max_blocks ? want_blocks : max_blocks), SHAPER_THREADS, SHAPER_SMEM, c->stream>>>(
             d_tx, origin, (int64_t)(first_bit + off), nb, cf, bit_en, d_g, (int32_t)noise_var, (uint4 *)(out_dev + off * 8));
         c->last_launches++;
         BBB_CUDA(c, cudaGetLastError());
