@@ -937,31 +937,67 @@ shaper_stream_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t f
 
 // RX decisions through the shaped channel: bit J is decided on the sample 8*(J+4)+delay (the pulse of
 // bit J peaks at tap 32), sliced at zero (rx.py:28); err word = decisions XOR transmitted bits.
+// One thread per 64 decisions.  The shaped sample of a bit period depends on 8 of the 9 window bits, so a CTA
+// tabulates it for the call's `delay` (256 int32, one copy per lane: conflict-free lookups); a thread then takes
+// its 73 window bits from three packed PRBS words and its 64 noise bytes with four 128-bit loads.
 __global__ void __launch_bounds__(256)
 shaped_slicer_err_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t first_bit, uint64_t nwords, ShaperCoef cf,
                          uint32_t delay, const int8_t *__restrict__ g, int32_t noise_var, uint64_t *__restrict__ err)
 {
-    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= nwords) return;
-    uint64_t e = 0;
-    for (uint32_t i = 0; i < 64; i++) {
-        const uint64_t r = j * 64 + i;
-        const int64_t J = first_bit + (int64_t)r + 4;          // the bit period the sample lies in
-        uint32_t win = 0;
-#pragma unroll
-        for (int q = 0; q < 9; q++) win |= tx_bit(txw, J - 8 + q, origin) << q;
+    __shared__ int32_t S[256 * 32];
+    {
+        const uint32_t idx = threadIdx.x;         // 256 threads: one pattern each
         int32_t a = 0;
 #pragma unroll
         for (int t = 0; t < 8; t++) {
+            // delay >= 4: tap 8t + delay - 4 of bit J - t (pattern bit 7 - t of win >> 1); else tap 8t + delay + 4 of bit J - 1 - t
             const int k = delay >= 4 ? 8 * t + (int)delay - 4 : 8 * t + (int)delay + 4;
-            const int q = delay >= 4 ? 8 - t : 7 - t;
             const int32_t c = cf.c[k];
-            a += ((win >> q) & 1u) ? c : -c;
+            a += ((idx >> (7 - t)) & 1u) ? c : -c;
         }
-        const int32_t x = a + (int32_t)g[r] * noise_var;          // g: the sampled phase only, one byte per bit
-        const int32_t x12 = ((x + 2048) & 4095) - 2048;
-        const uint32_t b = (win >> 4) & 1u;                    // b[J-4] = the bit being decided
-        e |= (uint64_t)((uint32_t)(x12 >= 0) ^ b) << i;
+#pragma unroll
+        for (int l = 0; l < 32; l++) S[idx * 32 + ((l + idx) & 31)] = a;
+    }
+    __syncthreads();
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nwords) return;
+    const int32_t *const Sl = S + (threadIdx.x & 31u);
+    const uint32_t wsh = delay >= 4 ? 1u : 0u;
+    uint64_t e = 0;
+    if (first_bit + (int64_t)(j * 64) < 4 || ((uintptr_t)g & 15)) {       // the start of time, bit by bit
+        for (uint32_t i = 0; i < 64; i++) {
+            const uint64_t r = j * 64 + i;
+            const int64_t J = first_bit + (int64_t)r + 4;          // the bit period the sample lies in
+            uint32_t win = 0;
+#pragma unroll
+            for (int q = 0; q < 9; q++) win |= tx_bit(txw, J - 8 + q, origin) << q;
+            const int32_t x = Sl[((win >> wsh) & 255u) * 32] + (int32_t)g[r] * noise_var;
+            const int32_t x12 = ((x + 2048) & 4095) - 2048;
+            e |= (uint64_t)((uint32_t)(x12 >= 0) ^ ((win >> 4) & 1u)) << i;   // b[J-4] = the bit being decided
+        }
+        err[j] = e;
+        return;
+    }
+    const uint64_t a0 = (uint64_t)(first_bit - 4 - origin) + j * 64;       // first window bit: b[J-8] of decision 0
+    const uint32_t sh = (uint32_t)(a0 & 63);
+    const uint64_t *wp = txw + (a0 >> 6);
+    const uint64_t w0 = wp[0], w1 = wp[1], w2 = sh > 55 ? wp[2] : 0ull;
+    const uint64_t B0 = sh ? (w0 >> sh) | (w1 << (64 - sh)) : w0;          // window bits 0..63
+    const uint64_t B1 = sh ? (w1 >> sh) | (w2 << (64 - sh)) : w1;          // window bits 64..
+    const uint4 *gp = (const uint4 *)(g + j * 64);
+#pragma unroll
+    for (uint32_t q = 0; q < 4; q++) {
+        const uint32_t V = (uint32_t)(q ? (B0 >> (16 * q)) | (B1 << (64 - 16 * q)) : B0);   // window bits 16q .. 16q+31
+        const uint4 v = __ldcs(gp + q);
+        const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (uint32_t i = 0; i < 16; i++) {
+            const uint32_t win = V >> i;
+            const int32_t nz = (int32_t)(int8_t)((vv[i >> 2] >> (8 * (i & 3))) & 0xffu) * noise_var;
+            const int32_t x = Sl[((win >> wsh) & 255u) * 32] + nz;
+            const int32_t x12 = ((x + 2048) & 4095) - 2048;
+            e |= (uint64_t)((uint32_t)(x12 >= 0) ^ ((win >> 4) & 1u)) << (16 * q + i);
+        }
     }
     err[j] = e;
 }

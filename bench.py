@@ -225,6 +225,26 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                                                             args.spb, args.log2_bits))
         dtype = "u32 GF(2) + int8/int32"
         l2 = "intermediate buffer = the one kept noise sample per bit (%d MiB per pass) exceeds L2" % (min(nbits, 1 << 32) >> 20)
+    elif w == "prbs_shaped_slicer":
+        # single-GPU composite: shaped TX word + noise -> slicer at sample `delay` -> detector
+        from basebandboard_b200 import shaper
+        nbits = 1 << args.log2_bits
+        ctx.lutopt_load_shipped(N_STATE)
+        coeff = shaper.tx_sets()[16]
+        def step():
+            det = lib.DetState(0, 1, (1 << args.k) - 1, 0)
+            extra["ctr"] = ctx.prbs_shaped_slicer_detect(args.k, nbits, coeff, init=1, noise_var=args.noise_var, delay=4, det=det)
+            extra["rounds"] = ctx.last_rounds
+            return ctx.last_launches
+        def step_e2e():
+            step()
+            return nbits, ctx.last_h2d_bytes + 48 + 128, ctx.last_d2h_bytes
+        units, metric, unit, scale = nbits, "prbs_shaped_slicer_gbit_per_s", "Gbit/s", 1e-9
+        workload = ("PRBS-%d through PRBSShaper set 16 + CLT-GRNG(n256) x %d (12-bit TX word, 8 samples/bit) -> slicer at "
+                    "sample 4 -> error detector, 2^%d bits per GPU (SURVEY 8f-3; replicas, not shards)"
+                    % (args.k, args.noise_var, args.log2_bits))
+        dtype = "u32 GF(2) + int8/int32"
+        l2 = "intermediate buffer = the one kept noise sample per bit (%d MiB per pass) exceeds L2" % (min(nbits, 1 << 32) >> 20)
     elif w == "tx_stream":
         from basebandboard_b200 import shaper
         nbits = 1 << (args.log2_bits - 7)                 # 16 B per bit: 2^36 "bits" of budget = 8 GiB of TX words
@@ -382,7 +402,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--log2-samples", type=int, default=40)
     ap.add_argument("--workload", default="clt_fused",
-                    choices=["clt_fused", "prbs_stream", "prbs_detect", "rnghunt", "prbs_slicer", "clt_stream", "tx_stream"],
+                    choices=["clt_fused", "prbs_stream", "prbs_detect", "rnghunt", "prbs_slicer", "prbs_shaped_slicer", "clt_stream",
+                             "tx_stream"],
                     help="clt_fused = the headline (BASELINE.json configs[2]); the others are the remaining "
                          "BASELINE configs, same JSON contract, their own metric")
     ap.add_argument("--k", type=int, default=31, help="PRBS order for the prbs_* workloads")
