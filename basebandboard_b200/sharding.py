@@ -123,6 +123,71 @@ def prbs_detect_sharded(engine, k, nbits, m=0, seed=1, first_bit=0, make_det=Non
     return dict(zip(keys, (int(v) for v in tot))), final, runs
 
 
+def _loop_sharded(run, spec_state, k, nbits, first_bit, warm_bits=1024):
+    """Shared shape of the sharded detector loops: contiguous word-aligned shards, a speculative start state per
+    rank, all-gather of (start, end) states, re-run of the ranks whose start differs from the left neighbour's
+    end, until consistent (= the sequential result, by induction from rank 0).  `run(lo, cnt, start)` returns
+    (counters dict, end state tuple).  Speculation for rank > 0: run the `warm_bits` bits before the shard from
+    the error-free locked state -- exact unless the detector was reloading just there."""
+    rank, world = rank_world()
+    words = (nbits + 63) // 64
+    wlo, wcnt = split_range(0, words, rank, world)
+    lo = first_bit + 64 * wlo
+    cnt = max(0, min(64 * wcnt, first_bit + nbits - lo))
+    reset = (0, 1, (1 << k) - 1, 0)                   # reset values, prbs.py:62,80,90
+    zero = {"err": 0, "err_valid": 0, "reload_events": 0, "reload_cycles": 0, "injected": 0}
+    if rank == 0 or lo - first_bit < warm_bits + 64 or lo - warm_bits < 64:
+        # short ranges: the chain from the true start is as cheap as a guess
+        start = reset if lo == first_bit else run(first_bit, lo - first_bit, reset)[1]
+    else:
+        start = run(lo - warm_bits, warm_bits, _det_tuple(spec_state(k, lo - warm_bits)))[1]
+    runs = 0
+    while True:
+        ctr, end = run(lo, cnt, start) if cnt else (zero, start)
+        runs += 1
+        table = _all_gather_i64(list(start) + list(end))     # [world, 8]
+        wrong = [r for r in range(1, world) if tuple(table[r][:4]) != tuple(table[r - 1][4:])]
+        if not wrong:
+            break
+        if rank in wrong:
+            start = tuple(int(v) for v in table[rank - 1][4:])
+    keys = ("err", "err_valid", "reload_events", "reload_cycles", "injected")
+    tot = _all_reduce_sum_u64(np.array([ctr[key] for key in keys], dtype=np.uint64))
+    final = tuple(int(v) for v in table[world - 1][4:])
+    return dict(zip(keys, (int(v) for v in tot))), final, runs
+
+
+def prbs_slicer_detect_sharded(engine, k, nbits, init=1, amplitude=256, noise_var=8, spb=8, delay=0, first_bit=0,
+                               make_det=None):
+    """The TX noise word -> slicer -> PRBSErrorDetector loop (tx.py:70-81, rx.py:28-46) over bits
+    [first_bit, first_bit+nbits) cut contiguously over the ranks; PRBS and noise are indexed by absolute bit,
+    so a shard is just the engine's call with its own first_bit.  Returns (counters, final state, runs)."""
+    if make_det is None:
+        from .lib import DetState as make_det
+
+    def run(lo, cnt, start):
+        det = make_det(*start)
+        ctr = engine.prbs_slicer_detect(k, cnt, init=init, amplitude=amplitude, noise_var=noise_var, spb=spb,
+                                        delay=delay, first_bit=lo, det=det)
+        return ctr, _det_tuple(det)
+
+    return _loop_sharded(run, lambda kk, at: engine.prbs_spec_state(kk, at, 0, 1), k, nbits, first_bit)
+
+
+def prbs_shaped_slicer_detect_sharded(engine, k, nbits, coeff, init=1, noise_var=8, delay=4, first_bit=0, make_det=None):
+    """Same for the pulse-shaped channel (bitshaper.py, bbb_prbs_shaped_slicer_detect)."""
+    if make_det is None:
+        from .lib import DetState as make_det
+
+    def run(lo, cnt, start):
+        det = make_det(*start)
+        ctr = engine.prbs_shaped_slicer_detect(k, cnt, coeff, init=init, noise_var=noise_var, delay=delay,
+                                               first_bit=lo, det=det)
+        return ctr, _det_tuple(det)
+
+    return _loop_sharded(run, lambda kk, at: engine.prbs_spec_state(kk, at, 0, 1), k, nbits, first_bit)
+
+
 def rnghunt_sweep_sharded(engine, n, seed, first, count, k=16):
     """Sweep candidates first .. first+count-1, rank r taking every world-th one; returns the k
     smallest accepted candidate indices overall and the summed stage counts."""

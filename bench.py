@@ -207,13 +207,19 @@ def run_secondary(args, ctx, rank, world, local_rank):
         dtype = "u32/u64 integer"
         l2 = "no HBM-resident input"
     elif w == "prbs_slicer":
-        # single-GPU composite; ranks run independent replicas of the same range
+        # SURVEY 8f-1 composite; rank r owns bits [r*2^b, (r+1)*2^b) (PRBS and noise are indexed by absolute bit) and
+        # starts from the detector state a 1024-bit warm-up window leaves (sharding._loop_sharded's speculation)
         nbits = 1 << args.log2_bits
+        first = rank * nbits
         ctx.lutopt_load_shipped(N_STATE)
         def step():
             det = lib.DetState(0, 1, (1 << args.k) - 1, 0)
+            if rank:
+                det = lib.DetState(*sharding._det_tuple(lib.prbs_spec_state(args.k, first - 1024, 0, 1)))
+                ctx.prbs_slicer_detect(args.k, 1024, init=1, amplitude=args.amplitude, noise_var=args.noise_var,
+                                       spb=args.spb, delay=0, first_bit=first - 1024, det=det)
             extra["ctr"] = ctx.prbs_slicer_detect(args.k, nbits, init=1, amplitude=args.amplitude, noise_var=args.noise_var,
-                                                  spb=args.spb, delay=0, det=det)
+                                                  spb=args.spb, delay=0, first_bit=first, det=det)
             extra["rounds"] = ctx.last_rounds
             return ctx.last_launches
         def step_e2e():
@@ -221,19 +227,25 @@ def run_secondary(args, ctx, rank, world, local_rank):
             return nbits, ctx.last_h2d_bytes + 48, ctx.last_d2h_bytes
         units, metric, unit, scale = nbits, "prbs_slicer_gbit_per_s", "Gbit/s", 1e-9
         workload = ("PRBS-%d -> +-%d + CLT-GRNG(n256) x %d (12-bit TX word, %d samples/bit) -> slicer -> error detector, "
-                    "2^%d bits per GPU (SURVEY 8f-1; replicas, not shards)" % (args.k, args.amplitude, args.noise_var,
+                    "2^%d bits per GPU (SURVEY 8f-1; contiguous bit ranges per rank)" % (args.k, args.amplitude, args.noise_var,
                                                                             args.spb, args.log2_bits))
         dtype = "u32 GF(2) + int8/int32"
         l2 = "intermediate buffer = the one kept noise sample per bit (%d MiB per pass) exceeds L2" % (min(nbits, 1 << 32) >> 20)
     elif w == "prbs_shaped_slicer":
-        # single-GPU composite: shaped TX word + noise -> slicer at sample `delay` -> detector
+        # SURVEY 8f-3 composite: shaped TX word + noise -> slicer at sample `delay` -> detector; ranks as for prbs_slicer
         from basebandboard_b200 import shaper
         nbits = 1 << args.log2_bits
+        first = rank * nbits
         ctx.lutopt_load_shipped(N_STATE)
         coeff = shaper.tx_sets()[16]
         def step():
             det = lib.DetState(0, 1, (1 << args.k) - 1, 0)
-            extra["ctr"] = ctx.prbs_shaped_slicer_detect(args.k, nbits, coeff, init=1, noise_var=args.noise_var, delay=4, det=det)
+            if rank:
+                det = lib.DetState(*sharding._det_tuple(lib.prbs_spec_state(args.k, first - 1024, 0, 1)))
+                ctx.prbs_shaped_slicer_detect(args.k, 1024, coeff, init=1, noise_var=args.noise_var, delay=4,
+                                              first_bit=first - 1024, det=det)
+            extra["ctr"] = ctx.prbs_shaped_slicer_detect(args.k, nbits, coeff, init=1, noise_var=args.noise_var, delay=4,
+                                                         first_bit=first, det=det)
             extra["rounds"] = ctx.last_rounds
             return ctx.last_launches
         def step_e2e():
@@ -241,7 +253,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
             return nbits, ctx.last_h2d_bytes + 48 + 128, ctx.last_d2h_bytes
         units, metric, unit, scale = nbits, "prbs_shaped_slicer_gbit_per_s", "Gbit/s", 1e-9
         workload = ("PRBS-%d through PRBSShaper set 16 + CLT-GRNG(n256) x %d (12-bit TX word, 8 samples/bit) -> slicer at "
-                    "sample 4 -> error detector, 2^%d bits per GPU (SURVEY 8f-3; replicas, not shards)"
+                    "sample 4 -> error detector, 2^%d bits per GPU (SURVEY 8f-3; contiguous bit ranges per rank)"
                     % (args.k, args.noise_var, args.log2_bits))
         dtype = "u32 GF(2) + int8/int32"
         l2 = "intermediate buffer = the one kept noise sample per bit (%d MiB per pass) exceeds L2" % (min(nbits, 1 << 32) >> 20)
@@ -295,6 +307,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
         dtype = "u32 GF(2)"
         l2 = "no HBM-resident input"
 
+    lop3_peak = max(ctx.measure_lop3_peak() for _ in range(3)) / 1e12 if w in ("prbs_slicer", "prbs_shaped_slicer") else None
     for _ in range(args.warmup):
         step()
         ctx.sync()
@@ -345,6 +358,18 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                 "peak": None, "frac": None, "traffic": None,
                                 "hbm_write_gbs": units * (2 if args.noise_var_stream >= 0 else 1) / (dev_ms / args.steps * 1e-3) / 1e9,
                                 "note": "986 LOP3 per 32 samples as for the fused kernel; HBM write rate given for reference"}
+        if w in ("prbs_slicer", "prbs_shaped_slicer"):
+            # dominant kernel clt256_dec: spb recurrence clocks (492 LOP3 each) + one CLT tree (494) per bit and 32 lanes
+            spb_ = args.spb if w == "prbs_slicer" else 8
+            per_bit = (spb_ * 492 + 494) / 32.0
+            ach = value / world * 1e9 * per_bit / 1e12
+            line["roofline"] = {"bound": "alu", "kernel": "clt256_dec", "achieved": ach, "peak": lop3_peak,
+                                "unit": "T thread-instr/s (LOP3-equivalent)", "frac": ach / lop3_peak if lop3_peak else None,
+                                "traffic": None,
+                                "note": "algorithmic work per bit = (spb x 492 recurrence + 494 popcount-tree LOP3) / 32 lanes; "
+                                        "peak = LOP3 issue rate measured live (bbb_measure_lop3_peak); ncu: the kernel's "
+                                        "shared-memory pipe is the busier one (82 % of its wavefront peak, ALU 75 %), "
+                                        "profiles/r1_dec_kernels_ncu_full.txt"}
         if "ctr" in extra:
             line["result_check"] = dict(extra["ctr"], rounds=extra["rounds"])
         if w == "rnghunt":

@@ -34,6 +34,15 @@ class OracleEngine:
         ctr, _, _ = self.O.prbs_detect(k, nbits, m=m, seed=seed, first_bit=first_bit, det=det)
         return ctr
 
+    def prbs_slicer_detect(self, k, nbits, init=1, amplitude=256, noise_var=8, spb=8, delay=0, first_bit=0, det=None):
+        """tx.py:70-81 + rx.py:28-46 composed from the oracle's pieces, as tests/test_gpu_prbs.py does."""
+        O = self.O
+        g = O.clt_run(self.rec.packed(self.n), init, first_bit * spb, nbits * spb, model=0, want=("out8",))["out8"]
+        tx, _ = O.prbs_bits(k, nbits, state=O.lib().orc_prbs_advance(k, 1, first_bit))
+        rx = O.slicer_rx_bits(tx, g, nbits, amplitude, noise_var, spb, delay)
+        ctr, _ = O.det_run_bits(k, rx, nbits, tx_words=tx, det=det)
+        return ctr
+
     def rnghunt_sweep(self, n, seed, first, count, k=16, stride=1):
         counts = np.zeros(5, dtype=np.uint64)
         best = []
@@ -43,6 +52,10 @@ class OracleEngine:
             if st[0] == 4:
                 best.append(first + i * stride)
         return {"best": best[:k], "stage_counts": counts}
+
+
+# quiet channel (the warm-up window gives the exact start state), and one in permanent reload storms
+SLICER_CASES = {"slicer_quiet": (15, 64 * 300, 300, 8), "slicer_storm": (7, 64 * 200, 40, 15)}
 
 
 def _worker(rank, world, port, q):
@@ -62,6 +75,9 @@ def _worker(rank, world, port, q):
                                 "det_mid": (15, 40000, 3)}.items():
         ctr, final, runs = sharding.prbs_detect_sharded(eng, k, nbits, m=m, seed=1, make_det=O.DetState)
         out[name] = (ctr, final, runs)
+    for name, (k, nbits, amp, nv) in SLICER_CASES.items():
+        out[name] = sharding.prbs_slicer_detect_sharded(eng, k, nbits, amplitude=amp, noise_var=nv, spb=4, delay=1,
+                                                        first_bit=128, make_det=O.DetState)
     r = sharding.rnghunt_sweep_sharded(eng, 16, 1, 100, 900, k=5)
     out["hunt"] = (r["best"], r["stage_counts"].tolist())
     out["stream"] = sharding.stream_shard(128, 1000003)
@@ -98,6 +114,7 @@ def test_sharded_results_equal_one_shot_oracle(orc, world):
     stages, counts = orc.rnghunt_sweep(16, 1, 100, 900, threads=4)
     want_best = [100 + int(i) for i in np.nonzero(stages == 4)[0]][:5]
     any_rerun = False
+    eng = OracleEngine()
     for rank in range(world):
         out = res[rank]
         assert out["clt"] == want_clt
@@ -110,6 +127,15 @@ def test_sharded_results_equal_one_shot_oracle(orc, world):
             if name == "det_low":
                 assert runs == 1
             any_rerun |= runs > 1
+        for name, (k, nbits, amp, nv) in SLICER_CASES.items():
+            det = orc.DetState()
+            orc.lib().orc_det_reset(k, __import__("ctypes").byref(det))
+            wctr = eng.prbs_slicer_detect(k, nbits, amplitude=amp, noise_var=nv, spb=4, delay=1, first_bit=128, det=det)
+            ctr, final, runs = out[name]
+            assert ctr == wctr, (name, rank)
+            assert final == (det.bit_in, det.prbs, det.err_sr, det.reload_ctr)
+            if name == "slicer_storm":
+                assert wctr["reload_events"] > 5
         assert out["hunt"] == (want_best, counts.tolist())
     assert any_rerun          # the hand-off path really ran
     # stream shards tile the range exactly
