@@ -558,7 +558,11 @@ def main():
             "gpu_launches": launches,
             "roofline": {"bound": "alu", "kernel": kernel_name, "achieved": achieved / 1e12, "peak": lop3_peak / 1e12,
                          "unit": "T thread-instr/s (LOP3-equivalent)", "frac": achieved / lop3_peak,
-                         "traffic": None, "launch_ms": one_call_ms,
+                         "traffic": 38887680 if kernel_name == "clt256_fused2" else None,
+                         "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one clt256_hist2_kernel launch "
+                                         "(ncu --set full, profiles/r1_clt256_fused2_ncu_full.txt): the 256 seed planes "
+                                         "x 37888 threads x 4 B, read once per launch whatever the sample count; 0 B written",
+                         "launch_ms": one_call_ms,
                          "note": "integer-pipe bound, not HBM/tensor: algorithmic work = 986 LOP3 per 32 "
                                  "samples (492 recurrence + 494 popcount tree); peak = LOP3 issue rate measured "
                                  "live on this GPU (bbb_measure_lop3_peak); HBM traffic ~0 B/sample"},

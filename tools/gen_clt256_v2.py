@@ -283,8 +283,13 @@ def main():
     emw, _ = body_hist_v2(rows, pos, resident, shape, "words")
     tail8, _ = tail_lines(shape, "s8")
     emp, _ = body_hist_v2(rows, pos, resident, shape, "plain")
-    out = os.path.join(ROOT, "basebandboard_b200", "csrc", "clt256_v2_gen.inc")
-    with open(out, "w") as f:
+    # CLT256V2_OUT / CLT256V2_PREFIX: a second instance with its own settings and macro prefix (the decimated-stream
+    # kernel's bodies, clt256_dec_gen.inc, are generated with more resident planes: tools/gen_clt256_dec.sh)
+    out = os.environ.get("CLT256V2_OUT") or os.path.join(ROOT, "basebandboard_b200", "csrc", "clt256_v2_gen.inc")
+    prefix = os.environ.get("CLT256V2_PREFIX", "CLT256V2")
+    import io
+    real_out, f = out, io.StringIO()
+    if True:
         f.write("// GENERATED by tools/gen_clt256_v2.py -- do not edit.  One-pass LUTOPT(n256) clock + CLTGRNG popcount\n")
         f.write("// network + histogram indices on 32 bit-sliced streams (rng.py:38-40, :96-105; rng_recurrences.py:172-259).\n")
         f.write("// recurrence LOP3: %d, carry-save adders: %d, half adders: %d, modelled peak live values: %d, lead %d, resident %d\n"
@@ -312,6 +317,8 @@ def main():
         f.write("\n#endif\n#ifdef CLT256V2_SECTION_P_BODY\n// the clock alone: no popcount network, nothing emitted (decimated sample streams)\n")
         f.write("\n".join(emp.lines))
         f.write("\n#endif\n")
+    with open(real_out, "w") as g:
+        g.write(f.getvalue().replace("CLT256V2_", prefix + "_"))
     print("wrote", out, "ops", em.ops, "peak live", peak, "resident", len(resident), file=sys.stderr)
 
 
