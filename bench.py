@@ -425,7 +425,8 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--log2-samples", type=int, default=40)
+    ap.add_argument("--log2-samples", type=int, default=None,
+                    help="samples per GPU: default 2^40 for clt_fused, 2^33 (int8) / 2^32 (int16) = 8 GiB for clt_stream")
     ap.add_argument("--workload", default="clt_fused",
                     choices=["clt_fused", "prbs_stream", "prbs_detect", "rnghunt", "prbs_slicer", "prbs_shaped_slicer", "clt_stream",
                              "tx_stream"],
@@ -446,6 +447,8 @@ def main():
     ap.add_argument("--tune", action="append", default=[], metavar="KEY=VALUE",
                     help="bbb_set_tuning knob (experiments only), e.g. clt_spec_variant=1")
     args = ap.parse_args()
+    if args.log2_samples is None:
+        args.log2_samples = 40 if args.workload != "clt_stream" else (32 if args.noise_var_stream >= 0 else 33)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
