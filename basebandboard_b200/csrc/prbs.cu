@@ -187,16 +187,29 @@ prbs_stream_kernel(const PrbsTables *__restrict__ tab, uint32_t s_first, uint64_
     if (cbase >= nwords) return;
     uint64_t h[K][VEC];
     {
-        uint32_t s = jump<K>(sh, s_first, (cbase + (uint64_t)VEC * lane) << 6);
+        // History = the chunk's first K*GW words.  Only the first K come from jump-ahead (lane l: word l); the
+        // rest follow from the word recurrence W[j] = W[j - K*2^e] ^ W[j - TAP*2^e], valid for every power of two
+        // (Frobenius), applied in the warp's shared buffer with the largest stride the known prefix allows, so a
+        // pass extends the prefix by TAP*2^e words at once (a handful of passes instead of K matrix products
+        // and 2K word look-ups per lane: the seeding was 0.10 ms of a 64 MB call).
+        extern __shared__ uint64_t prbs_wbuf[];
+        uint64_t *const wb = prbs_wbuf + (size_t)(threadIdx.x >> 5) * (K * GW);
+        if (lane < K) wb[lane] = word_of<K>(sh, jump<K>(sh, s_first, (cbase + lane) << 6));
+        __syncwarp();
+        constexpr uint32_t TOTAL = K * GW;
+        uint32_t have = K, e = 0;
+        while (have < TOTAL) {
+            while (((uint32_t)K << (e + 1)) <= have) e++;
+            const uint32_t dk = (uint32_t)K << e, dt = (uint32_t)TAP << e;
+            const uint32_t batch = dt < TOTAL - have ? dt : TOTAL - have;
+            for (uint32_t i = lane; i < batch; i += 32) wb[have + i] = wb[have + i - dk] ^ wb[have + i - dt];
+            __syncwarp();
+            have += batch;
+        }
 #pragma unroll
         for (int m = 0; m < K; m++) {
-            uint32_t sv = s;
 #pragma unroll
-            for (int v = 0; v < VEC; v++) {
-                h[m][v] = word_of<K>(sh, sv);
-                sv = state_after<K>(h[m][v]);
-            }
-            s = matvec<K>(sh.pw[6 + LOG_GW], s);          // GW words further on
+            for (int v = 0; v < VEC; v++) h[m][v] = wb[m * GW + VEC * lane + v];
         }
     }
     uint64_t j = cbase + (uint64_t)VEC * lane;
@@ -426,8 +439,11 @@ static int launch_stream(bbb_ctx *c, uint32_t k, const PrbsTables *dtab, uint32_
     const uint64_t blocks = (warps + 3) / 4;
     if (blocks > 0x7fffffffull) return c->fail(BBB_EINVAL, "range too large");
 #define PRBS_CASE(K, TAP) \
-    case K: prbs_stream_kernel<K, TAP, VEC><<<(uint32_t)blocks, 128, 0, c->stream>>>(dtab, s_first, nwords, \
-                                                                                      (uint32_t)reps, d_out); break
+    case K: \
+        BBB_CUDA(c, cudaFuncSetAttribute(prbs_stream_kernel<K, TAP, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                         4 * K * 32 * VEC * 8)); \
+        prbs_stream_kernel<K, TAP, VEC><<<(uint32_t)blocks, 128, 4 * K * 32 * VEC * 8, c->stream>>>(dtab, s_first, nwords, \
+                                                                                                     (uint32_t)reps, d_out); break
     switch (k) {
         PRBS_CASE(7, 6); PRBS_CASE(9, 5); PRBS_CASE(11, 9); PRBS_CASE(15, 14);
         PRBS_CASE(20, 3); PRBS_CASE(23, 18); PRBS_CASE(31, 28);
