@@ -307,7 +307,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
         dtype = "u32 GF(2)"
         l2 = "no HBM-resident input"
 
-    lop3_peak = max(ctx.measure_lop3_peak() for _ in range(3)) / 1e12 if w in ("prbs_slicer", "prbs_shaped_slicer") else None
+    lop3_peak = max(ctx.measure_lop3_peak() for _ in range(3)) / 1e12 if w in ("prbs_slicer", "prbs_shaped_slicer", "clt_stream") else None
     for _ in range(args.warmup):
         step()
         ctx.sync()
@@ -354,10 +354,12 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                         "(MEASURED_PEAKS.json), per GPU"}
         if w == "clt_stream":
             # still integer-pipe bound when stored (30.8 thread-instr per byte), SURVEY 8d
-            line["roofline"] = {"bound": "alu", "achieved": value / world * 1e9 * 30.8125 / 1e12, "unit": "T thread-instr/s (LOP3-equivalent)",
-                                "peak": None, "frac": None, "traffic": None,
+            ach = value / world * 1e9 * 30.8125 / 1e12
+            line["roofline"] = {"bound": "alu", "kernel": "clt256_s8v2", "achieved": ach, "unit": "T thread-instr/s (LOP3-equivalent)",
+                                "peak": lop3_peak, "frac": ach / lop3_peak if lop3_peak else None, "traffic": None,
                                 "hbm_write_gbs": units * (2 if args.noise_var_stream >= 0 else 1) / (dev_ms / args.steps * 1e-3) / 1e9,
-                                "note": "986 LOP3 per 32 samples as for the fused kernel; HBM write rate given for reference"}
+                                "note": "986 LOP3 per 32 samples as for the fused kernel; peak = LOP3 issue rate measured live "
+                                        "(bbb_measure_lop3_peak); HBM write rate given for reference"}
         if w in ("prbs_slicer", "prbs_shaped_slicer"):
             # dominant kernel clt256_dec: spb recurrence clocks (492 LOP3 each) + one CLT tree (494) per bit and 32 lanes
             spb_ = args.spb if w == "prbs_slicer" else 8
