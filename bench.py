@@ -343,8 +343,13 @@ def run_secondary(args, ctx, rank, world, local_rank):
                 "gpu_launches": launches}
         if w == "tx_stream" and hbm_peak:
             ach = units / (dev_ms / args.steps * 1e-3) / 1e9
-            line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                                "traffic": None, "note": "algorithmic bytes = 16 B written per PRBS bit (8 int16 TX words); "
+            line["roofline"] = {"bound": "hbm", "kernel": "shaper_stream", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                                "frac": ach / hbm_peak,
+                                "traffic": 8617702000 if args.log2_bits == 36 else None,
+                                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one shaper_stream_kernel launch at "
+                                                "2^29 bits (ncu --set full, profiles/r1_shaper_stream_ncu_full.txt): 8.55 GB written "
+                                                "for 8.59 GB of TX words, 68 MB read (the packed PRBS words)",
+                                "note": "algorithmic bytes = 16 B written per PRBS bit (8 int16 TX words); "
                                 "peak = measured copy bandwidth (MEASURED_PEAKS.json), per GPU"}
         if w == "prbs_stream" and hbm_peak:
             ach = units / 8 / (dev_ms / args.steps * 1e-3) / 1e9
