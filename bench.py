@@ -353,8 +353,12 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                 "peak = measured copy bandwidth (MEASURED_PEAKS.json), per GPU"}
         if w == "prbs_stream" and hbm_peak:
             ach = units / 8 / (dev_ms / args.steps * 1e-3) / 1e9
-            line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
-                                "frac": ach / hbm_peak, "traffic": None,
+            line["roofline"] = {"bound": "hbm", "kernel": "prbs_stream", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                                "frac": ach / hbm_peak,
+                                "traffic": 8529677576 if (args.log2_bits == 36 and args.k == 31) else None,
+                                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of the 2^36-bit prbs_stream_kernel "
+                                                "launch (ncu --set full, profiles/r1_prbs_stream_ncu_full.txt): 8.53 GB written "
+                                                "for 8.59 GB of packed bits (the last lines are still in L2 at kernel end), 0.1 MB read",
                                 "note": "algorithmic bytes = 1/8 B per PRBS bit; peak = measured copy bandwidth "
                                         "(MEASURED_PEAKS.json), per GPU"}
         if w == "clt_stream":
