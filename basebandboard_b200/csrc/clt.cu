@@ -498,7 +498,7 @@ int bbb_clt_run_decimated(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64
             uint64_t blocks = rem / (spbk * 32);
             if (blocks > max_blocks) blocks = max_blocks;
             uint64_t Ld = blocks ? rem / (blocks * spbk) : 0;
-            if (Ld > (1ull << 26)) Ld = 1ull << 26;
+            if (Ld > (1ull << 31) / spb) Ld = (1ull << 31) / spb;   // clocks per stream (Ld * spb) stay below 2^32
             Ld &= ~31ull;                                   // 32 sampled clocks per flush (one full sector per stream)
             if (blocks >= 1 && Ld >= 32) {
                 const uint64_t S = blocks * spbk, L = Ld * spb;
