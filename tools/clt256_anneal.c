@@ -12,6 +12,8 @@
 #define N 256
 static int ntap[N], tap[N][4];
 static int lead_g = 0;
+static double w_elig = 0.0;   // reward per plane that can stay in a register across the loop edge (short wraps first)
+static int done_t[N];
 
 static uint64_t rng_s = 88172645463325252ull;
 static inline uint64_t rnd64(void)
@@ -50,6 +52,7 @@ static double cost(const int *pos, int *peak_out, double *mean_out)
         for (int i = 0; i < k && i < 3; i++)
             if (death[ts[i]] < fold) death[ts[i]] = fold;
         int done = ts[k - 1];
+        done_t[r] = done;
         if (k == 4 && ts[3] > ts[2]) {
             diff[ts[2]]++;
             diff[ts[3]]--;
@@ -77,7 +80,11 @@ static double cost(const int *pos, int *peak_out, double *mean_out)
     }
     if (peak_out) *peak_out = peak;
     if (mean_out) *mean_out = sum / (double)N;
-    return peak + p4 / 64.0;
+    double elig = 0;
+    if (w_elig > 0)
+        for (int r = 0; r < N; r++)
+            if (done_t[r] > death[pos[r]]) elig += 1.0 - (double)(N - done_t[r] + pos[r]) / (2.0 * N);
+    return peak + p4 / 64.0 - w_elig * elig;
 }
 
 int main(int argc, char **argv)
@@ -85,6 +92,7 @@ int main(int argc, char **argv)
     long iters = argc > 1 ? atol(argv[1]) : 1000000;
     if (argc > 2) rng_s ^= (uint64_t)atol(argv[2]) * 0x9E3779B97F4A7C15ull;
     if (argc > 3) lead_g = atoi(argv[3]);
+    if (argc > 4) w_elig = atof(argv[4]);
     for (int r = 0; r < N; r++) {
         if (scanf("%d", &ntap[r]) != 1) return 1;
         for (int i = 0; i < ntap[r]; i++)
