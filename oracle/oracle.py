@@ -128,6 +128,7 @@ def lib():
                                    C.c_uint32, C.c_uint64, P(DetCounters)]),
         "orc_rnghunt_candidate": (_BMat, [C.c_uint32, C.c_uint64, C.c_uint64]),
         "orc_rnghunt_eval": (C.c_int, [bmp, u64p, C.c_uint32]),
+        "orc_rnghunt_eval_list": (None, [C.c_uint32, C.c_uint64, u64p, C.c_uint64, u8p, u64p, C.c_int]),
         "orc_rnghunt_sweep": (None, [C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64, u8p, u64p,
                                      C.c_int]),
     }
@@ -504,6 +505,17 @@ def rnghunt_sweep(n, seed, first, count, threads=1):
     counts = np.zeros(5, dtype=np.uint64)
     lib().orc_rnghunt_sweep(n, seed, first, count, stages.ctypes.data_as(C.POINTER(C.c_uint8)),
                             _u64p(counts), threads)
+    return stages, counts
+
+
+def rnghunt_eval_list(n, seed, cands, threads=1):
+    """Stage of every candidate index in `cands` (rnghunt.rs:27-44 on candidate c of `seed`)."""
+    idx = np.ascontiguousarray(cands, dtype=np.uint64)
+    stages = np.zeros(idx.size, dtype=np.uint8)
+    counts = np.zeros(5, dtype=np.uint64)
+    if idx.size:
+        lib().orc_rnghunt_eval_list(n, seed, _u64p(idx), idx.size, stages.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                    _u64p(counts), threads)
     return stages, counts
 
 

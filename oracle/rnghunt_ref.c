@@ -91,6 +91,7 @@ int orc_rnghunt_eval(const bmat *a, uint64_t *poly_words, uint32_t poly_cap_word
 
 typedef struct {
     uint32_t n; uint64_t seed, first, count; int tid, nthreads;
+    const uint64_t *list;          /* candidate indices, or NULL for first + i */
     uint8_t *stage_out; uint64_t stages[ORC_NSTAGES];
 } sweep_job;
 
@@ -98,7 +99,7 @@ static void *sweep_worker(void *arg)
 {
     sweep_job *j = (sweep_job *)arg;
     for (uint64_t i = (uint64_t)j->tid; i < j->count; i += (uint64_t)j->nthreads) {
-        bmat a = orc_rnghunt_candidate(j->n, j->seed, j->first + i);
+        bmat a = orc_rnghunt_candidate(j->n, j->seed, j->list ? j->list[i] : j->first + i);
         int st = orc_rnghunt_eval(&a, NULL, 0);
         bm_free(&a);
         j->stages[st] += 1;
@@ -107,8 +108,23 @@ static void *sweep_worker(void *arg)
     return NULL;
 }
 
+static void sweep_run(uint32_t n, uint64_t seed, uint64_t first, const uint64_t *list, uint64_t count,
+                      uint8_t *stage_out, uint64_t *stage_counts, int threads);
+
 void orc_rnghunt_sweep(uint32_t n, uint64_t seed, uint64_t first, uint64_t count,
                        uint8_t *stage_out, uint64_t *stage_counts, int threads)
+{
+    sweep_run(n, seed, first, NULL, count, stage_out, stage_counts, threads);
+}
+
+void orc_rnghunt_eval_list(uint32_t n, uint64_t seed, const uint64_t *cands, uint64_t count,
+                           uint8_t *stage_out, uint64_t *stage_counts, int threads)
+{
+    sweep_run(n, seed, 0, cands, count, stage_out, stage_counts, threads);
+}
+
+static void sweep_run(uint32_t n, uint64_t seed, uint64_t first, const uint64_t *list, uint64_t count,
+                      uint8_t *stage_out, uint64_t *stage_counts, int threads)
 {
     if (threads < 1) threads = 1;
     sweep_job *jobs = (sweep_job *)calloc((size_t)threads, sizeof(sweep_job));
@@ -116,7 +132,7 @@ void orc_rnghunt_sweep(uint32_t n, uint64_t seed, uint64_t first, uint64_t count
     for (int t = 0; t < threads; t++) {
         sweep_job *j = &jobs[t];
         j->n = n; j->seed = seed; j->first = first; j->count = count;
-        j->tid = t; j->nthreads = threads; j->stage_out = stage_out;
+        j->tid = t; j->nthreads = threads; j->stage_out = stage_out; j->list = list;
         pthread_create(&tid[t], NULL, sweep_worker, j);
     }
     for (int t = 0; t < threads; t++) {

@@ -30,6 +30,10 @@ int orc_rnghunt_eval(const bmat *a, uint64_t *poly_words, uint32_t poly_cap_word
 void orc_rnghunt_sweep(uint32_t n, uint64_t seed, uint64_t first, uint64_t count,
                        uint8_t *stage_out, uint64_t *stage_counts, int threads);
 
+/* The same verdicts for an arbitrary list of candidate indices of `seed`. */
+void orc_rnghunt_eval_list(uint32_t n, uint64_t seed, const uint64_t *cands, uint64_t count,
+                           uint8_t *stage_out, uint64_t *stage_counts, int threads);
+
 #ifdef __cplusplus
 }
 #endif
