@@ -182,45 +182,57 @@ struct HuntOut {
     uint64_t *poly_out;        // [count][ceil((n+1)/64)] reference layout, or null
 };
 
+// a[idx] for a register array and a run-time index (0 when idx is out of range): a select chain, so the
+// array never goes to local memory
+template <int N>
+__device__ __forceinline__ uint32_t reg_pick(const uint32_t (&a)[N], uint32_t idx)
+{
+    uint32_t r = 0;
+#pragma unroll
+    for (int k = 0; k < N; k++) r = (uint32_t)k == idx ? a[k] : r;
+    return r;
+}
+
 // Degree / filter verdict of one candidate and, for survivors, its polynomial.
 // c: connection polynomial bits c_j (the reference's coefficient j, highest power first).
 template <int NWP>
-__device__ __forceinline__ void hunt_finish(const HuntOut &o, uint32_t n, uint32_t slot, const uint32_t (&creg)[NWP],
+__device__ __forceinline__ void hunt_finish(const HuntOut &o, uint32_t n, uint32_t slot, const uint32_t (&c)[NWP],
                                          uint32_t l)
 {
     const uint32_t pw64 = (n + 1 + 63) / 64;
-    uint32_t c[NWP];   // a copy the dynamic indexing below may spill without touching the caller's registers
-#pragma unroll
-    for (int w = 0; w < NWP; w++) c[w] = creg[w];
     if (o.poly_out) {
         // BinaryPolynomial words: coefficient j at word j/64, bit 63 - j%64 (binary_vector.rs:25-31)
-        for (uint32_t w = 0; w < pw64; w++) {
-            uint64_t v = 0;
-            if (l == n) {
-                const uint32_t lo = 2 * w < (uint32_t)NWP ? c[2 * w] : 0u;
-                const uint32_t hi = 2 * w + 1 < (uint32_t)NWP ? c[2 * w + 1] : 0u;
-                v = __brevll(((uint64_t)hi << 32) | lo);
+#pragma unroll
+        for (int w = 0; w < (NWP + 1) / 2; w++) {
+            if ((uint32_t)w < pw64) {
+                uint64_t v = 0;
+                if (l == n) {
+                    const uint32_t lo = c[2 * w];
+                    const uint32_t hi = 2 * w + 1 < NWP ? c[2 * w + 1 < NWP ? 2 * w + 1 : 0] : 0u;
+                    v = __brevll(((uint64_t)hi << 32) | lo);
+                }
+                o.poly_out[(size_t)slot * pw64 + w] = v;
             }
-            o.poly_out[(size_t)slot * pw64 + w] = v;
         }
     }
     if (l != n) { o.stage[slot] = BBB_STAGE_DEGREE; return; }               // rnghunt.rs:39-41
     uint32_t ones = 0;
 #pragma unroll
     for (int w = 0; w < NWP; w++) ones += __popc(c[w]);
-    const uint32_t cn = (c[n >> 5] >> (n & 31)) & 1u;                       // constant term = c_n
+    const uint32_t cn = (reg_pick<NWP>(c, n >> 5) >> (n & 31)) & 1u;        // constant term = c_n
     if (!cn || !(ones & 1u)) { o.stage[slot] = BBB_STAGE_FILTER; return; }  // binary_polynomial.rs:185-192
     o.stage[slot] = HUNT_PENDING;
     const uint32_t s = atomicAdd(o.surv_count, 1u);
     o.surv_cand[s] = slot;
-    // p(x) = sum c_j x^(n-j): reverse the n+1 coefficient bits
+    // p(x) = sum c_j x^(n-j): reverse the whole register array, then shift the n+1 coefficients down
+    uint32_t rev[NWP];
+#pragma unroll
+    for (int w = 0; w < NWP; w++) rev[w] = __brev(c[NWP - 1 - w]);
+    const uint32_t sh = 32u * NWP - 1u - n, ws = sh >> 5, bs = sh & 31u;
     uint32_t *dst = o.surv_poly + (size_t)s * NWP;
-    for (int w = 0; w < NWP; w++) dst[w] = 0;
-    for (uint32_t j = 0; j <= n; j++) {
-        const uint32_t b = (c[j >> 5] >> (j & 31)) & 1u;
-        const uint32_t i = n - j;
-        dst[i >> 5] |= b << (i & 31);
-    }
+#pragma unroll
+    for (int w = 0; w < NWP; w++)
+        dst[w] = __funnelshift_r(reg_pick<NWP>(rev, (uint32_t)w + ws), reg_pick<NWP>(rev, (uint32_t)w + ws + 1u), bs);
 }
 
 __device__ __forceinline__ uint32_t lds_u8(uint32_t sa)
@@ -257,7 +269,6 @@ struct FrontParams {
     uint32_t count;
     HuntOut out;
     uint16_t *dump_taps;   // [n][4] taps of candidate `first` (bbb_rnghunt_candidate), else null
-    uint32_t *gtaps;       // [n][count] packed taps, scratch of hunt_front_reg_kernel
 };
 
 // shared memory: state bytes xs[(n+1)][B] words, then taps[n][B] (4 x TapT per thread and row)
@@ -334,61 +345,108 @@ __global__ void hunt_front_kernel(FrontParams p)
 }
 
 // ---------------------------------------------------------------------------
-// front kernel with the tap lists in REGISTERS (n <= 32*NW <= 192): the row loop is fully unrolled,
-// row r's four column indices are the bytes of register tp[r]; shared memory holds only the state
-// bytes, so twice as many warps fit on an SM and a row costs no tap load.  The generator hands the
-// taps over through a global scratch array (written and read once, coalesced).
+// front kernel, one WARP per candidate (n <= 256): the product path.
+//
+// The state x (n bits = NW words) is replicated in every lane; lane l owns rows l, l+32, ... and keeps
+// each of them as NW mask words (bit c of word w set = column 32w+c is a tap of the row), so a row is
+// NW LOP3 ((W & M) ^ acc) + one parity, and the NW ballots of a step ARE the new state words (lane l's
+// vote in ballot j = row l+32j): no gather, no shared-memory traffic and no per-step address arithmetic.
+// A step costs NW*NW + 3*NW warp instructions for all n rows, where the thread-per-candidate kernel
+// spends 16 instructions per row and thread (4 LDS.U8 gathers + 1 STS.U8 per row, shared-memory bound).
+//
+// BinaryMatrix::random and Berlekamp-Massey are sequential per candidate, so they run thread-per-
+// candidate around the warp phase: CPW lanes generate CPW candidates (taps go to shared memory, one
+// word per row, an empty fourth slot repeating the third pick), the warp then clocks the candidates one
+// after the other and leaves each one's 2n output bits in shared memory, and finally lane c runs the
+// online Berlekamp-Massey over candidate c's bits.  Nothing but the verdict (and the polynomial of the
+// few survivors) goes to global memory.
+// shared: taps[n][CPW+1] words, seq[ceil(2n/32)][CPW] words
 // ---------------------------------------------------------------------------
-template <int NW>
+template <int NW, int CPW>
 __global__ void __launch_bounds__(32, 8)
-hunt_front_reg_kernel(FrontParams p)
+hunt_front_warp_kernel(FrontParams p)
 {
     constexpr int NWP = NW + 1;
-    constexpr uint32_t NR = 32 * NW;
+    constexpr uint32_t TS = CPW + 1;                       // odd stride: conflict-free both ways
     extern __shared__ uint32_t hsm[];
-    const uint32_t B = 32, tid = threadIdx.x, n = p.n;
-    const uint32_t slot = blockIdx.x * B + tid;
-    if (slot >= p.count) return;
-    const uint64_t cand = p.first + (uint64_t)slot * p.stride;
-    {
-        uint32_t acc = 0;
+    const uint32_t lane = threadIdx.x, n = p.n;
+    const uint32_t slot0 = blockIdx.x * CPW;
+    if (slot0 >= p.count) return;
+    const uint32_t ncand = p.count - slot0 < (uint32_t)CPW ? p.count - slot0 : (uint32_t)CPW;
+    const uint32_t SW = (2 * n + 31) / 32;                 // sequence words per candidate (<= 2 NW)
+    uint32_t *taps = hsm;
+    uint32_t *seq = hsm + (size_t)n * TS;
+
+    // phase 1: lane c generates candidate slot0 + c (binary_matrix.rs:81-101)
+    if (lane < ncand) {
+        const uint64_t cand = p.first + (uint64_t)(slot0 + lane) * p.stride;
+        uint32_t acc = 0, prev = 0;
         hunt_generate<NW>(n, p.seed, cand, [&](uint32_t row, uint32_t k, uint32_t col) {
-            acc |= col << (8 * k);
-            if (k == 3) { p.gtaps[(size_t)row * p.count + slot] = acc; acc = 0; }
+            const uint32_t cc = col == n ? prev : col;     // empty slot: repeat the previous pick (masks are ORed)
+            prev = cc;
+            acc |= cc << (8 * k);
+            if (k == 3) { taps[row * TS + lane] = acc; acc = 0; }
         });
     }
-    uint32_t tp[NR];
-#pragma unroll
-    for (uint32_t r = 0; r < NR; r++) tp[r] = r < n ? p.gtaps[(size_t)r * p.count + slot] : 0u;
+    __syncwarp();
 
-    uint32_t *xs = hsm;
-    for (uint32_t i = 0; i < n; i++) xs[i * B + tid] = 1u;     // b = all ones (rnghunt.rs:28)
-    xs[n * B + tid] = 0u;                                       // row n: what empty tap slots read
-    const uint32_t xs_sa = (uint32_t)__cvta_generic_to_shared(xs + tid);
-    constexpr uint32_t rs = 4 * 32;
-    HuntBM<NWP> bm;
-    bm.init();
-#pragma unroll 1
-    for (uint32_t step = 0; step < 2 * n; step++) {
-        const uint32_t xo = xs_sa + (step & 3), xn = xs_sa + ((step + 1) & 3);
+    // phase 2: the warp clocks one candidate at a time (binary_matrix.rs:68-76 from b = all ones, rnghunt.rs:28-29)
+    for (uint32_t c = 0; c < ncand; c++) {
+        uint32_t M[NW][NW];
 #pragma unroll
-        for (uint32_t r0 = 0; r0 < NR; r0 += 8) {
-            if (r0 < n) {                                       // warp-uniform
-                uint32_t v[8];
+        for (int j = 0; j < NW; j++) {
 #pragma unroll
-                for (uint32_t k = 0; k < 8; k++)
-                    v[k] = lds_u8(tap_byte(tp[r0 + k], 0x4440u) * rs + xo) ^
-                           lds_u8(tap_byte(tp[r0 + k], 0x4441u) * rs + xo) ^
-                           lds_u8(tap_byte(tp[r0 + k], 0x4442u) * rs + xo) ^
-                           lds_u8(tap_byte(tp[r0 + k], 0x4443u) * rs + xo);
+            for (int w = 0; w < NW; w++) M[j][w] = 0;
+            const uint32_t row = lane + 32u * j;
+            if (row < n) {
+                const uint32_t t4 = taps[row * TS + c];
 #pragma unroll
-                for (uint32_t k = 0; k < 8; k++)
-                    if (r0 + k < n) sts_u8(xn + (r0 + k) * rs, v[k]);
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t t = (t4 >> (8 * k)) & 0xffu, bit = 1u << (t & 31u);
+#pragma unroll
+                    for (int w = 0; w < NW; w++) M[j][w] |= (t >> 5) == (uint32_t)w ? bit : 0u;
+                }
             }
         }
-        bm.push(lds_u8(xn));
+        uint32_t W[NW];
+#pragma unroll
+        for (int w = 0; w < NW; w++) {
+            const uint32_t lo = (uint32_t)w * 32u;
+            W[w] = n >= lo + 32 ? 0xffffffffu : (n > lo ? (1u << (n - lo)) - 1u : 0u);
+        }
+        uint32_t acc = 0, mine = 0;
+        for (uint32_t ch = 0; ch < SW; ch++) {
+#pragma unroll 4
+            for (int st = 0; st < 32; st++) {
+                uint32_t Wn[NW];
+#pragma unroll
+                for (int j = 0; j < NW; j++) {
+                    uint32_t v = W[0] & M[j][0];
+#pragma unroll
+                    for (int w = 1; w < NW; w++) v ^= W[w] & M[j][w];
+                    Wn[j] = __ballot_sync(0xffffffffu, __popc(v) & 1u);
+                }
+#pragma unroll
+                for (int w = 0; w < NW; w++) W[w] = Wn[w];
+                acc = (acc << 1) | (W[0] & 1u);            // x[0] after the step (binary_matrix.rs:73); first bit ends on top
+            }
+            if (lane == ch) mine = acc;
+        }
+        if (lane < SW) seq[lane * CPW + c] = mine;
     }
-    hunt_finish<NWP>(p.out, n, slot, bm.c, bm.l);
+    __syncwarp();
+
+    // phase 3: lane c runs Berlekamp-Massey over candidate c's 2n bits (berlekamp_massey.rs:5-31)
+    if (lane < ncand) {
+        HuntBM<NWP> bm;
+        bm.init();
+        for (uint32_t ch = 0; ch < SW; ch++) {
+            const uint32_t word = seq[ch * CPW + lane];
+            const uint32_t nb = 2 * n - 32 * ch < 32u ? 2 * n - 32 * ch : 32u;
+            for (uint32_t st = 0; st < nb; st++) bm.push((word >> (31u - st)) & 1u);
+        }
+        hunt_finish<NWP>(p.out, n, slot0 + lane, bm.c, bm.l);
+    }
 }
 
 // ---------------------------------------------------------------------------
