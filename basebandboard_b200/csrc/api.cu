@@ -94,6 +94,23 @@ void *bbb_ctx::scratch(int slot, size_t bytes)
     return d_scratch[slot];
 }
 
+void *bbb_ctx::pinned(int slot, size_t bytes)
+{
+    if (bytes <= pinned_bytes[slot] && h_pinned[slot]) return h_pinned[slot];
+    if (h_pinned[slot]) cudaFreeHost(h_pinned[slot]);
+    h_pinned[slot] = nullptr;
+    pinned_bytes[slot] = 0;
+    size_t want = bytes < 4096 ? 4096 : bytes;
+    cudaError_t e = cudaHostAlloc(&h_pinned[slot], want, cudaHostAllocPortable | cudaHostAllocMapped);
+    if (e != cudaSuccess) {
+        cuda_fail(e, "cudaHostAlloc(pinned)");
+        h_pinned[slot] = nullptr;
+        return nullptr;
+    }
+    pinned_bytes[slot] = want;
+    return h_pinned[slot];
+}
+
 void bbb_ctx::begin_call()
 {
     if (nest) return;      // inside a composite call: one timing region, counters keep adding up
@@ -154,6 +171,11 @@ int bbb_create(int device, bbb_ctx **out)
     if (prop.major < 10) { delete c; return BBB_EUNSUPPORTED; }   // built for sm_100a only
     c->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_slot[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_slot[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
         cudaEventCreate(&c->evt0) != cudaSuccess || cudaEventCreate(&c->evt1) != cudaSuccess) {
         delete c;
@@ -168,7 +190,13 @@ void bbb_destroy(bbb_ctx *c)
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    if (c->stream2) cudaStreamSynchronize(c->stream2);
     for (int i = 0; i < 16; i++) if (c->d_scratch[i]) cudaFree(c->d_scratch[i]);
+    for (int i = 0; i < 4; i++) if (c->h_pinned[i]) cudaFreeHost(c->h_pinned[i]);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
+    for (int i = 0; i < 2; i++) if (c->ev_slot[i]) cudaEventDestroy(c->ev_slot[i]);
+    if (c->stream2) cudaStreamDestroy(c->stream2);
     if (c->d_row_ptr) cudaFree(c->d_row_ptr);
     if (c->d_taps) cudaFree(c->d_taps);
     bbb_prbs_free_tables(c);
@@ -213,6 +241,7 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
     else if (!strcmp(key, "hunt_smem_taps")) c->tune_hunt_smem_taps = (int)value;
     else if (!strcmp(key, "hunt_slow_check")) c->tune_hunt_slow_check = value != 0;
     else if (!strcmp(key, "hunt_batch")) c->tune_hunt_batch = value < 0 ? 0u : (uint32_t)value;
+    else if (!strcmp(key, "hunt_cpw")) c->tune_hunt_cpw = value == 16 ? 16u : 0u;
     else if (!strcmp(key, "prbs_stream_reps")) c->tune_prbs_stream_reps = value < 0 ? 0u : (uint32_t)value;
     else return c->fail(BBB_EINVAL, "unknown tuning key %s", key);
     return BBB_OK;

@@ -35,7 +35,9 @@ struct HostMat {
 struct bbb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;    // second queue: overlapped batches (rnghunt) and chunked D2H copies (streams)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evt0 = nullptr, evt1 = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_slot[2] = {nullptr, nullptr};
     uint64_t h2d_bytes = 0, d2h_bytes = 0;
     int sm_count = 0;
     std::string err;
@@ -61,6 +63,7 @@ struct bbb_ctx {
     int tune_hunt_smem_taps = 0;        // 1: never use the taps-in-registers front kernel
     int tune_hunt_slow_check = 0;       // 1: always use the shift-and-add primitivity kernel
     uint32_t tune_hunt_batch = 0;       // 0: 2^20 candidates per rnghunt batch
+    uint32_t tune_hunt_cpw = 0;         // candidates per warp pass of hunt_front_warp_kernel: 0/32, or 16
     uint32_t last_rounds = 0;           // kernel rounds of the last bbb_prbs_detect
     // PRBS jump tables per k (prbs.cu), built on first use
     void *prbs_host[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -86,6 +89,10 @@ struct bbb_ctx {
     int fail(int code, const char *fmt, ...);
     int cuda_fail(cudaError_t e, const char *what);
     void *scratch(int slot, size_t bytes);   // nullptr on failure (err set)
+    // pinned (page-locked, device-visible) host buffers, grown on demand
+    void *h_pinned[4] = {};
+    size_t pinned_bytes[4] = {};
+    void *pinned(int slot, size_t bytes);    // nullptr on failure (err set)
     // counted copies on the ctx's stream
     cudaError_t h2d(void *dst, const void *src, size_t bytes)
     {

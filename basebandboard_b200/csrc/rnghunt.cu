@@ -538,8 +538,9 @@ __device__ __forceinline__ void poly_square(uint32_t (&r)[NWP], const uint32_t (
 }
 
 struct CheckParams {
-    uint32_t n, nitems, nexp;          // nexp exponents per polynomial in this launch
+    uint32_t n, nexp;                  // nexp exponents per polynomial in this launch
     uint32_t exp_first;                // index of the first exponent (0 = 2^n-1, i >= 1 = cofactor i)
+    const uint32_t *npoly;             // device: how many polynomials (survivors, or order passers)
     const uint32_t *poly_index;        // [npoly] survivor index of polynomial q, or null = identity
     const uint32_t *polys;             // [..][NWP]
     const uint64_t *exp_words;         // all exponents of n back to back, MS word first
@@ -547,38 +548,41 @@ struct CheckParams {
     uint32_t *result;                  // [survivor] bit (exp index) set when x^e == 1
 };
 
+// The item counts live on the device (the front kernel's survivor counter, the compaction's pass counter), so
+// the host never waits for them: every check launch is a fixed grid striding over *npoly * nexp items.
 template <int NWP>
 __global__ void __launch_bounds__(128)
 hunt_check_kernel(CheckParams q)
 {
-    const uint32_t item = blockIdx.x * blockDim.x + threadIdx.x;
-    if (item >= q.nitems) return;
-    const uint32_t pi = item / q.nexp, ei = q.exp_first + item % q.nexp;
-    const uint32_t sidx = q.poly_index ? q.poly_index[pi] : pi;
-    uint32_t p[NWP], r[NWP];
+    const uint32_t nitems = *q.npoly * q.nexp;
+    for (uint32_t item = blockIdx.x * blockDim.x + threadIdx.x; item < nitems; item += gridDim.x * blockDim.x) {
+        const uint32_t pi = item / q.nexp, ei = q.exp_first + item % q.nexp;
+        const uint32_t sidx = q.poly_index ? q.poly_index[pi] : pi;
+        uint32_t p[NWP], r[NWP];
 #pragma unroll
-    for (int w = 0; w < NWP; w++) { p[w] = q.polys[(size_t)sidx * NWP + w]; r[w] = 0; }
-    r[0] = 1;                                              // modexp starts from 1 (:138-142)
-    const uint64_t *e = q.exp_words + q.exp_off[ei];
-    const uint32_t ew = q.exp_off[ei + 1] - q.exp_off[ei];
-    bool started = false;
-    for (uint32_t w = 0; w < ew; w++) {
-        const uint64_t word = e[w];
-        for (int b = 63; b >= 0; b--) {
-            const uint32_t bit = (uint32_t)(word >> b) & 1u;
-            if (!started) {
-                if (!bit) continue;                        // 1 squared stays 1
-                started = true;
-            } else {
-                poly_square<NWP>(r, p, q.n);
+        for (int w = 0; w < NWP; w++) { p[w] = q.polys[(size_t)sidx * NWP + w]; r[w] = 0; }
+        r[0] = 1;                                              // modexp starts from 1 (:138-142)
+        const uint64_t *e = q.exp_words + q.exp_off[ei];
+        const uint32_t ew = q.exp_off[ei + 1] - q.exp_off[ei];
+        bool started = false;
+        for (uint32_t w = 0; w < ew; w++) {
+            const uint64_t word = e[w];
+            for (int b = 63; b >= 0; b--) {
+                const uint32_t bit = (uint32_t)(word >> b) & 1u;
+                if (!started) {
+                    if (!bit) continue;                        // 1 squared stays 1
+                    started = true;
+                } else {
+                    poly_square<NWP>(r, p, q.n);
+                }
+                if (bit) poly_mulx<NWP>(r, p, q.n);
             }
-            if (bit) poly_mulx<NWP>(r, p, q.n);
         }
-    }
-    uint32_t rest = r[0] ^ 1u;
+        uint32_t rest = r[0] ^ 1u;
 #pragma unroll
-    for (int w = 1; w < NWP; w++) rest |= r[w];
-    if (rest == 0) atomicOr(&q.result[sidx], 1u << (ei > 31 ? 31 : ei));
+        for (int w = 1; w < NWP; w++) rest |= r[w];
+        if (rest == 0) atomicOr(&q.result[sidx], 1u << (ei > 31 ? 31 : ei));
+    }
 }
 
 // The same test for n = 32*NW with a per-polynomial table R_j = x^(n+j) mod p, j < 32, in shared
@@ -600,94 +604,106 @@ hunt_check32_kernel(CheckParams q, uint32_t stride)
 {
     extern __shared__ uint32_t rsm[];
     const uint32_t B = blockDim.x, tid = threadIdx.x;
-    const uint32_t item = blockIdx.x * B + tid;
-    if (item >= q.nitems) return;
-    const uint32_t pi = item / q.nexp, ei = q.exp_first + item % q.nexp;
-    const uint32_t sidx = q.poly_index ? q.poly_index[pi] : pi;
+    const uint32_t nitems = *q.npoly * q.nexp;
     uint32_t *const R = rsm + tid;
-    uint32_t pl[NW], r[NW];                        // p without its leading term = x^n mod p
+    for (uint32_t item = blockIdx.x * B + tid; item < nitems; item += gridDim.x * B) {
+        const uint32_t pi = item / q.nexp, ei = q.exp_first + item % q.nexp;
+        const uint32_t sidx = q.poly_index ? q.poly_index[pi] : pi;
+        uint32_t pl[NW], r[NW];                        // p without its leading term = x^n mod p
 #pragma unroll
-    for (int w = 0; w < NW; w++) pl[w] = q.polys[(size_t)sidx * stride + w];
-    {
-        uint32_t t[NW];
+        for (int w = 0; w < NW; w++) pl[w] = q.polys[(size_t)sidx * stride + w];
+        {
+            uint32_t t[NW];
 #pragma unroll
-        for (int w = 0; w < NW; w++) t[w] = pl[w];
-        for (uint32_t j = 0; j < 32; j++) {
+            for (int w = 0; w < NW; w++) t[w] = pl[w];
+            for (uint32_t j = 0; j < 32; j++) {
 #pragma unroll
-            for (int w = 0; w < NW; w++) R[(j * NW + w) * B] = t[w];
-            const uint32_t m = 0u - (t[NW - 1] >> 31);
+                for (int w = 0; w < NW; w++) R[(j * NW + w) * B] = t[w];
+                const uint32_t m = 0u - (t[NW - 1] >> 31);
 #pragma unroll
-            for (int w = NW - 1; w > 0; w--) t[w] = ((t[w] << 1) | (t[w - 1] >> 31)) ^ (pl[w] & m);
-            t[0] = (t[0] << 1) ^ (pl[0] & m);
+                for (int w = NW - 1; w > 0; w--) t[w] = ((t[w] << 1) | (t[w - 1] >> 31)) ^ (pl[w] & m);
+                t[0] = (t[0] << 1) ^ (pl[0] & m);
+            }
         }
-    }
 #pragma unroll
-    for (int w = 0; w < NW; w++) r[w] = 0;
-    r[0] = 1;
-    const uint64_t *e = q.exp_words + q.exp_off[ei];
-    const uint32_t ew = q.exp_off[ei + 1] - q.exp_off[ei];
-    bool started = false;
-    for (uint32_t wi = 0; wi < ew; wi++) {
-        const uint64_t word = e[wi];
-        for (int b = 63; b >= 0; b--) {
-            const uint32_t bit = (uint32_t)(word >> b) & 1u;
-            if (!started) {
-                if (!bit) continue;
-                started = true;
-            } else {
-                uint32_t V[2 * NW];
+        for (int w = 0; w < NW; w++) r[w] = 0;
+        r[0] = 1;
+        const uint64_t *e = q.exp_words + q.exp_off[ei];
+        const uint32_t ew = q.exp_off[ei + 1] - q.exp_off[ei];
+        bool started = false;
+        for (uint32_t wi = 0; wi < ew; wi++) {
+            const uint64_t word = e[wi];
+            for (int b = 63; b >= 0; b--) {
+                const uint32_t bit = (uint32_t)(word >> b) & 1u;
+                if (!started) {
+                    if (!bit) continue;
+                    started = true;
+                } else {
+                    uint32_t V[2 * NW];
 #pragma unroll
-                for (int w = 0; w < NW; w++) { V[2 * w] = spread16(r[w]); V[2 * w + 1] = spread16(r[w] >> 16); }
+                    for (int w = 0; w < NW; w++) { V[2 * w] = spread16(r[w]); V[2 * w + 1] = spread16(r[w] >> 16); }
 #pragma unroll
-                for (int qq = NW - 1; qq >= 0; qq--) {
-                    uint32_t chunk = V[NW + qq];               // coefficients of x^(n+32qq+j)
-                    while (chunk) {
-                        const uint32_t j = __ffs(chunk) - 1;
-                        chunk &= chunk - 1;
-                        const uint32_t *Rj = R + (size_t)j * NW * B;
+                    for (int qq = NW - 1; qq >= 0; qq--) {
+                        uint32_t chunk = V[NW + qq];               // coefficients of x^(n+32qq+j)
+                        while (chunk) {
+                            const uint32_t j = __ffs(chunk) - 1;
+                            chunk &= chunk - 1;
+                            const uint32_t *Rj = R + (size_t)j * NW * B;
 #pragma unroll
-                        for (int w = 0; w < NW; w++) V[qq + w] ^= Rj[w * B];
+                            for (int w = 0; w < NW; w++) V[qq + w] ^= Rj[w * B];
+                        }
                     }
+#pragma unroll
+                    for (int w = 0; w < NW; w++) r[w] = V[w];
                 }
+                if (bit) {                                         // times x
+                    const uint32_t m = 0u - (r[NW - 1] >> 31);
 #pragma unroll
-                for (int w = 0; w < NW; w++) r[w] = V[w];
-            }
-            if (bit) {                                         // times x
-                const uint32_t m = 0u - (r[NW - 1] >> 31);
-#pragma unroll
-                for (int w = NW - 1; w > 0; w--) r[w] = ((r[w] << 1) | (r[w - 1] >> 31)) ^ (pl[w] & m);
-                r[0] = (r[0] << 1) ^ (pl[0] & m);
+                    for (int w = NW - 1; w > 0; w--) r[w] = ((r[w] << 1) | (r[w - 1] >> 31)) ^ (pl[w] & m);
+                    r[0] = (r[0] << 1) ^ (pl[0] & m);
+                }
             }
         }
-    }
-    uint32_t rest = r[0] ^ 1u;
+        uint32_t rest = r[0] ^ 1u;
 #pragma unroll
-    for (int w = 1; w < NW; w++) rest |= r[w];
-    if (rest == 0) atomicOr(&q.result[sidx], 1u << (ei > 31 ? 31 : ei));
+        for (int w = 1; w < NW; w++) rest |= r[w];
+        if (rest == 0) atomicOr(&q.result[sidx], 1u << (ei > 31 ? 31 : ei));
+    }
 }
 
 // survivors whose x^(2^n-1) == 1 go on to the cofactor tests (binary_polynomial.rs:198-208)
-__global__ void hunt_compact_kernel(const uint32_t *__restrict__ result, uint32_t nsurv, uint32_t *pass_count,
+__global__ void hunt_compact_kernel(const uint32_t *__restrict__ result, const uint32_t *nsurv_p, uint32_t *pass_count,
                                     uint32_t *pass_index)
 {
-    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= nsurv) return;
-    if (result[s] & 1u) pass_index[atomicAdd(pass_count, 1u)] = s;
+    const uint32_t nsurv = *nsurv_p;
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < nsurv; s += gridDim.x * blockDim.x)
+        if (result[s] & 1u) pass_index[atomicAdd(pass_count, 1u)] = s;
 }
 
+// Final stage of every survivor; accepted candidates go to the hit list, which lives in pinned HOST memory
+// (zero-copy: hits are rare, 1 in 2240 at n = 192) together with their polynomials when the caller wants them.
 __global__ void hunt_classify_kernel(const uint32_t *__restrict__ result, const uint32_t *__restrict__ surv_cand,
-                                     uint32_t nsurv, uint8_t *stage, uint32_t *hit_count, uint32_t *hits)
+                                     const uint32_t *nsurv_p, uint8_t *stage, uint32_t *hit_count, uint32_t hit_cap,
+                                     uint32_t *hits, const uint32_t *__restrict__ surv_poly, uint32_t nwp, uint32_t *hit_poly)
 {
-    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= nsurv) return;
-    const uint32_t r = result[s];
-    uint8_t st;
-    if (!(r & 1u)) st = BBB_STAGE_ORDER;
-    else if (r & ~1u) st = BBB_STAGE_FACTOR;
-    else st = BBB_STAGE_PRIMITIVE;
-    const uint32_t slot = surv_cand[s];
-    stage[slot] = st;
-    if (st == BBB_STAGE_PRIMITIVE) hits[atomicAdd(hit_count, 1u)] = slot;
+    const uint32_t nsurv = *nsurv_p;
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < nsurv; s += gridDim.x * blockDim.x) {
+        const uint32_t r = result[s];
+        uint8_t st;
+        if (!(r & 1u)) st = BBB_STAGE_ORDER;
+        else if (r & ~1u) st = BBB_STAGE_FACTOR;
+        else st = BBB_STAGE_PRIMITIVE;
+        const uint32_t slot = surv_cand[s];
+        stage[slot] = st;
+        if (st == BBB_STAGE_PRIMITIVE) {
+            const uint32_t h = atomicAdd(hit_count, 1u);
+            if (h < hit_cap) {
+                hits[h] = slot;
+                if (hit_poly)
+                    for (uint32_t w = 0; w < nwp; w++) hit_poly[(size_t)h * nwp + w] = surv_poly[(size_t)s * nwp + w];
+            }
+        }
+    }
 }
 
 __global__ void hunt_count_kernel(const uint8_t *__restrict__ stage, uint32_t count, unsigned long long *counts)
@@ -706,66 +722,101 @@ __global__ void hunt_count_kernel(const uint8_t *__restrict__ stage, uint32_t co
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
-struct HuntBuffers {
+// One batch in flight.  Two of them alternate between the ctx's two streams, so the short, badly filled
+// back-end kernels of batch i run beside the front kernel of batch i+1, and the host reads batch i's hit
+// list (pinned memory, written by the classify kernel) only after it has queued batch i+1.
+struct HuntSlot {
+    cudaStream_t stream;
+    cudaEvent_t done;
     uint8_t *stage;
-    uint32_t *counters;            // [0] survivors, [1] order passers, [2] hits
-    unsigned long long *counts;    // [BBB_NSTAGES]
-    uint32_t *surv_cand, *surv_poly, *result, *pass_index, *hits, *exp_off;
+    uint32_t *counters;            // device: [0] survivors, [1] order passers, [2] hits
+    uint32_t *surv_cand, *surv_poly, *result, *pass_index;
+    uint32_t *h_hdr;               // pinned host: copy of counters[0..3]
+    uint32_t *h_hits;              // pinned host, device-visible: [hit_cap] accepted slots
+    uint32_t *h_hit_poly;          // pinned host: [hit_cap][nwp], or null
+    uint32_t hit_cap;
+    uint64_t first;                // candidate index of slot 0
+    uint32_t nb;                   // candidates in the batch in flight (0 = idle)
+};
+
+struct HuntShared {
+    unsigned long long *counts;    // [BBB_NSTAGES], accumulated by both streams
+    uint32_t *exp_off;
     uint64_t *exp_words;
     uint32_t nf;                   // exponents for n (entry 0 = 2^n - 1)
 };
 
 static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
-// Carves scratch slot 6 for a batch of `cap` candidates and uploads the exponent table of n
-// (factors.rs:7-16: [2^n-1, (2^n-1)/q_1, ...], MS word first).
-static int hunt_buffers(bbb_ctx *c, uint32_t n, uint32_t cap, uint32_t nwp, HuntBuffers &b)
+// Carves scratch slot 6 (device) and pinned slot 0 (host) for `nslots` batches of `cap` candidates and uploads
+// the exponent table of n (factors.rs:7-16: [2^n-1, (2^n-1)/q_1, ...], MS word first).
+static int hunt_setup(bbb_ctx *c, uint32_t n, uint32_t cap, uint32_t nwp, bool want_polys, int nslots, HuntShared &sh,
+                      HuntSlot *slots)
 {
     const uint32_t e0 = BBB_MF_OFFSETS[n - 1], e1 = BBB_MF_OFFSETS[n];
-    b.nf = e1 - e0;
-    std::vector<uint32_t> off(b.nf + 1);
+    sh.nf = e1 - e0;
+    std::vector<uint32_t> off(sh.nf + 1);
     std::vector<uint64_t> words;
-    for (uint32_t i = 0; i < b.nf; i++) {
+    for (uint32_t i = 0; i < sh.nf; i++) {
         off[i] = (uint32_t)words.size();
         for (uint32_t w = BBB_MF_ENTRIES[e0 + i]; w < BBB_MF_ENTRIES[e0 + i + 1]; w++) words.push_back(BBB_MF_WORDS[w]);
     }
-    off[b.nf] = (uint32_t)words.size();
-    size_t at = 0;
+    off[sh.nf] = (uint32_t)words.size();
+    const uint32_t hit_cap = cap < 65536u ? cap : 65536u;
+    size_t at = 0, hat = 0;
     auto take = [&](size_t bytes) { size_t o = at; at += align256(bytes); return o; };
-    const size_t o_stage = take(cap), o_ctr = take(16), o_counts = take(8 * BBB_NSTAGES),
-                 o_cand = take((size_t)cap * 4), o_poly = take((size_t)cap * nwp * 4), o_res = take((size_t)cap * 4),
-                 o_pass = take((size_t)cap * 4), o_hits = take((size_t)cap * 4), o_eoff = take(off.size() * 4),
-                 o_ew = take(words.size() * 8);
+    auto htake = [&](size_t bytes) { size_t o = hat; hat += align256(bytes); return o; };
+    const size_t o_counts = take(8 * BBB_NSTAGES), o_eoff = take(off.size() * 4), o_ew = take(words.size() * 8);
+    size_t o_stage[2], o_ctr[2], o_cand[2], o_poly[2], o_res[2], o_pass[2], h_hdr[2], h_hits[2], h_poly[2];
+    for (int i = 0; i < nslots; i++) {
+        o_stage[i] = take(cap); o_ctr[i] = take(16); o_cand[i] = take((size_t)cap * 4);
+        o_poly[i] = take((size_t)cap * nwp * 4); o_res[i] = take((size_t)cap * 4); o_pass[i] = take((size_t)cap * 4);
+        h_hdr[i] = htake(16); h_hits[i] = htake((size_t)hit_cap * 4);
+        h_poly[i] = want_polys ? htake((size_t)hit_cap * nwp * 4) : 0;
+    }
     char *d = (char *)c->scratch(6, at);
-    if (!d) return BBB_ECUDA;
-    b.stage = (uint8_t *)(d + o_stage);
-    b.counters = (uint32_t *)(d + o_ctr);
-    b.counts = (unsigned long long *)(d + o_counts);
-    b.surv_cand = (uint32_t *)(d + o_cand);
-    b.surv_poly = (uint32_t *)(d + o_poly);
-    b.result = (uint32_t *)(d + o_res);
-    b.pass_index = (uint32_t *)(d + o_pass);
-    b.hits = (uint32_t *)(d + o_hits);
-    b.exp_off = (uint32_t *)(d + o_eoff);
-    b.exp_words = (uint64_t *)(d + o_ew);
-    BBB_CUDA(c, c->h2d(b.exp_off, off.data(), off.size() * 4));
-    BBB_CUDA(c, c->h2d(b.exp_words, words.data(), words.size() * 8));
+    char *h = (char *)c->pinned(0, hat);
+    if (!d || !h) return BBB_ECUDA;
+    sh.counts = (unsigned long long *)(d + o_counts);
+    sh.exp_off = (uint32_t *)(d + o_eoff);
+    sh.exp_words = (uint64_t *)(d + o_ew);
+    for (int i = 0; i < nslots; i++) {
+        HuntSlot &b = slots[i];
+        b.stream = i ? c->stream2 : c->stream;
+        b.done = c->ev_slot[i];
+        b.stage = (uint8_t *)(d + o_stage[i]);
+        b.counters = (uint32_t *)(d + o_ctr[i]);
+        b.surv_cand = (uint32_t *)(d + o_cand[i]);
+        b.surv_poly = (uint32_t *)(d + o_poly[i]);
+        b.result = (uint32_t *)(d + o_res[i]);
+        b.pass_index = (uint32_t *)(d + o_pass[i]);
+        b.h_hdr = (uint32_t *)(h + h_hdr[i]);
+        b.h_hits = (uint32_t *)(h + h_hits[i]);
+        b.h_hit_poly = want_polys ? (uint32_t *)(h + h_poly[i]) : nullptr;
+        b.hit_cap = hit_cap;
+        b.first = 0;
+        b.nb = 0;
+    }
+    BBB_CUDA(c, c->h2d(sh.exp_off, off.data(), off.size() * 4));
+    BBB_CUDA(c, c->h2d(sh.exp_words, words.data(), words.size() * 8));
+    BBB_CUDA(c, cudaMemsetAsync(sh.counts, 0, 8 * BBB_NSTAGES, c->stream));
     BBB_CUDA(c, cudaStreamSynchronize(c->stream));   // off / words are about to go out of scope
     return BBB_OK;
 }
 
-static int launch_check(bbb_ctx *c, uint32_t nwp, const CheckParams &q)
+static int launch_check(bbb_ctx *c, cudaStream_t st, uint32_t nwp, const CheckParams &q, uint64_t max_items)
 {
-    if (!q.nitems) return BBB_OK;
+    if (!max_items) return BBB_OK;
     if (q.n % 32 == 0 && !c->tune_hunt_slow_check) {
         const uint32_t nw = q.n / 32, B = 64;
         const size_t smem = (size_t)32 * nw * B * 4;
-        const uint32_t blocks = (q.nitems + B - 1) / B;
+        const uint64_t want = (max_items + B - 1) / B, most = (uint64_t)c->sm_count * (smem > 56 * 1024 ? 2 : 4);
+        const uint32_t blocks = (uint32_t)(want < most ? want : most);
 #define CHECK32_CASE(N)                                                                                        \
     case N:                                                                                                    \
         BBB_CUDA(c, cudaFuncSetAttribute(hunt_check32_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
                                          (int)smem));                                                          \
-        hunt_check32_kernel<N><<<blocks, B, smem, c->stream>>>(q, nwp);                                        \
+        hunt_check32_kernel<N><<<blocks, B, smem, st>>>(q, nwp);                                               \
         break
         switch (nw) {
             CHECK32_CASE(1); CHECK32_CASE(2); CHECK32_CASE(3); CHECK32_CASE(4); CHECK32_CASE(5); CHECK32_CASE(6);
@@ -778,8 +829,9 @@ static int launch_check(bbb_ctx *c, uint32_t nwp, const CheckParams &q)
         BBB_CUDA(c, cudaGetLastError());
         return BBB_OK;
     }
-    const uint32_t blocks = (q.nitems + 127) / 128;
-#define CHECK_CASE(N) case N: hunt_check_kernel<N><<<blocks, 128, 0, c->stream>>>(q); break
+    const uint64_t want = (max_items + 127) / 128, most = (uint64_t)c->sm_count * 8;
+    const uint32_t blocks = (uint32_t)(want < most ? want : most);
+#define CHECK_CASE(N) case N: hunt_check_kernel<N><<<blocks, 128, 0, st>>>(q); break
     switch (nwp) {
         CHECK_CASE(2); CHECK_CASE(3); CHECK_CASE(4); CHECK_CASE(5); CHECK_CASE(6); CHECK_CASE(7); CHECK_CASE(8);
         CHECK_CASE(9); CHECK_CASE(10); CHECK_CASE(11); CHECK_CASE(12); CHECK_CASE(13); CHECK_CASE(14);
@@ -792,76 +844,93 @@ static int launch_check(bbb_ctx *c, uint32_t nwp, const CheckParams &q)
     return BBB_OK;
 }
 
-// Stages 2 and 3 of the pipeline for the survivors the front kernel left in `b`; on return
-// b.stage holds the final verdict of every candidate of the batch, hits[] the accepted slots.
-static int hunt_back_end(bbb_ctx *c, uint32_t n, uint32_t count, uint32_t nwp, HuntBuffers &b,
-                         std::vector<uint32_t> &hit_slots)
+// Stages 2 and 3 of the pipeline for the survivors the front kernel left in `b`, queued on b.stream without a
+// single host round trip: the survivor / passer counts are read by the kernels themselves.  Afterwards b.stage
+// holds the final verdict of every candidate of the batch, the pinned hit list the accepted slots.
+static int hunt_back_end(bbb_ctx *c, uint32_t n, uint32_t nb, uint32_t nwp, const HuntShared &sh, HuntSlot &b)
 {
-    uint32_t ctr[3] = {0, 0, 0};
-    BBB_CUDA(c, c->d2h(ctr, b.counters, 4));
-    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
-    const uint32_t nsurv = ctr[0];
-    hit_slots.clear();
-    if (nsurv) {
-        BBB_CUDA(c, cudaMemsetAsync(b.result, 0, (size_t)nsurv * 4, c->stream));
-        CheckParams q;
-        q.n = n; q.polys = b.surv_poly; q.exp_words = b.exp_words; q.exp_off = b.exp_off; q.result = b.result;
-        q.nitems = nsurv; q.nexp = 1; q.exp_first = 0; q.poly_index = nullptr;            // x^(2^n-1) == 1 ?
-        int rc = launch_check(c, nwp, q);
-        if (rc) return rc;
-        const uint32_t gb = (nsurv + 255) / 256;
-        if (b.nf > 1) {
-            hunt_compact_kernel<<<gb, 256, 0, c->stream>>>(b.result, nsurv, b.counters + 1, b.pass_index);
-            c->last_launches++;
-            BBB_CUDA(c, c->d2h(ctr + 1, b.counters + 1, 4));
-            BBB_CUDA(c, cudaStreamSynchronize(c->stream));
-            const uint64_t items = (uint64_t)ctr[1] * (b.nf - 1);
-            if (items > 0xfffffff0ull) return c->fail(BBB_EINVAL, "batch too large");
-            q.nitems = (uint32_t)items; q.nexp = b.nf - 1; q.exp_first = 1; q.poly_index = b.pass_index;
-            rc = launch_check(c, nwp, q);                                                  // cofactors
-            if (rc) return rc;
-        }
-        hunt_classify_kernel<<<gb, 256, 0, c->stream>>>(b.result, b.surv_cand, nsurv, b.stage, b.counters + 2, b.hits);
+    cudaStream_t st = b.stream;
+    BBB_CUDA(c, cudaMemsetAsync(b.result, 0, (size_t)nb * 4, st));
+    CheckParams q;
+    q.n = n; q.polys = b.surv_poly; q.exp_words = sh.exp_words; q.exp_off = sh.exp_off; q.result = b.result;
+    q.npoly = b.counters; q.nexp = 1; q.exp_first = 0; q.poly_index = nullptr;            // x^(2^n-1) == 1 ?
+    int rc = launch_check(c, st, nwp, q, nb);
+    if (rc) return rc;
+    const uint32_t gb = std::min<uint32_t>((nb + 255) / 256, (uint32_t)c->sm_count * 4);
+    if (sh.nf > 1) {
+        hunt_compact_kernel<<<gb, 256, 0, st>>>(b.result, b.counters, b.counters + 1, b.pass_index);
         c->last_launches++;
-        BBB_CUDA(c, cudaGetLastError());
-        BBB_CUDA(c, c->d2h(ctr + 2, b.counters + 2, 4));
-        BBB_CUDA(c, cudaStreamSynchronize(c->stream));
-        if (ctr[2]) {
-            hit_slots.resize(ctr[2]);
-            BBB_CUDA(c, c->d2h(hit_slots.data(), b.hits, (size_t)ctr[2] * 4));
-            BBB_CUDA(c, cudaStreamSynchronize(c->stream));
-        }
+        q.npoly = b.counters + 1; q.nexp = sh.nf - 1; q.exp_first = 1; q.poly_index = b.pass_index;
+        rc = launch_check(c, st, nwp, q, (uint64_t)nb * (sh.nf - 1));                     // cofactors
+        if (rc) return rc;
     }
-    hunt_count_kernel<<<c->sm_count * 2, 256, 0, c->stream>>>(b.stage, count, b.counts);
-    c->last_launches++;
+    hunt_classify_kernel<<<gb, 256, 0, st>>>(b.result, b.surv_cand, b.counters, b.stage, b.counters + 2, b.hit_cap,
+                                            b.h_hits, b.surv_poly, nwp, b.h_hit_poly);
+    hunt_count_kernel<<<c->sm_count * 2, 256, 0, st>>>(b.stage, nb, sh.counts);
+    c->last_launches += 2;
     BBB_CUDA(c, cudaGetLastError());
+    BBB_CUDA(c, cudaMemcpyAsync(b.h_hdr, b.counters, 16, cudaMemcpyDeviceToHost, st));
+    c->d2h_bytes += 16;
+    BBB_CUDA(c, cudaEventRecord(b.done, st));
+    b.nb = nb;
     return BBB_OK;
 }
 
-static int launch_front(bbb_ctx *c, const FrontParams &p)
+struct HuntHit {
+    uint64_t cand;
+    std::vector<uint32_t> poly;    // nwp words, bit i = coefficient of x^i (empty unless requested)
+};
+
+// Waits for the batch in `b` and appends its accepted candidates.
+static int hunt_collect(bbb_ctx *c, HuntSlot &b, uint64_t stride, uint32_t nwp, std::vector<HuntHit> &found)
 {
-    const uint32_t n = p.n, nw = (n + 31) / 32, B = 32;
-    // taps in registers pay off once the shared-memory kernel is down to a few warps per SM (n > 128);
-    // "hunt_smem_taps" = 2 forces the register kernel for every n <= 192 (tests)
-    if (p.gtaps && nw <= 6 && (nw >= 5 ? c->tune_hunt_smem_taps != 1 : c->tune_hunt_smem_taps == 2)) {
-        const size_t smem = (size_t)B * (n + 1) * 4;
-        const uint32_t blocks = (p.count + B - 1) / B;
-#define FRONT_REG_CASE(NW)                                                                                \
-    case NW:                                                                                              \
-        BBB_CUDA(c, cudaFuncSetAttribute(hunt_front_reg_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                         (int)smem));                                                     \
-        hunt_front_reg_kernel<NW><<<blocks, B, smem, c->stream>>>(p);                                     \
+    if (!b.nb) return BBB_OK;
+    BBB_CUDA(c, cudaEventSynchronize(b.done));
+    const uint32_t nh = b.h_hdr[2];
+    b.nb = 0;
+    if (nh > b.hit_cap) return c->fail(BBB_EINVAL, "%u hits in one batch: lower hunt_batch", nh);
+    c->d2h_bytes += (uint64_t)nh * 4 * (b.h_hit_poly ? 1 + nwp : 1);
+    for (uint32_t i = 0; i < nh; i++) {
+        HuntHit h;
+        h.cand = b.first + (uint64_t)b.h_hits[i] * stride;
+        if (b.h_hit_poly) h.poly.assign(b.h_hit_poly + (size_t)i * nwp, b.h_hit_poly + (size_t)(i + 1) * nwp);
+        found.push_back(std::move(h));
+    }
+    return BBB_OK;
+}
+
+static int launch_front(bbb_ctx *c, cudaStream_t st, const FrontParams &p)
+{
+    const uint32_t n = p.n, nw = (n + 31) / 32;
+    // n <= 256: warp per candidate (state in registers, no gathers); "hunt_smem_taps" = 1 forces the
+    // thread-per-candidate kernel (tests: the two are independent implementations)
+    if (!p.dump_taps && nw <= 8 && c->tune_hunt_smem_taps != 1) {
+        const uint32_t cpw = c->tune_hunt_cpw == 16 ? 16 : 32;
+        const size_t smem = ((size_t)n * (cpw + 1) + (size_t)((2 * n + 31) / 32) * cpw) * 4;
+        const uint32_t blocks = (p.count + cpw - 1) / cpw;
+#define FRONT_WARP_CASE(NW)                                                                                         \
+    case NW:                                                                                                        \
+        if (cpw == 32) {                                                                                            \
+            BBB_CUDA(c, cudaFuncSetAttribute(hunt_front_warp_kernel<NW, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                             (int)smem));                                                           \
+            hunt_front_warp_kernel<NW, 32><<<blocks, 32, smem, st>>>(p);                                            \
+        } else {                                                                                                    \
+            BBB_CUDA(c, cudaFuncSetAttribute(hunt_front_warp_kernel<NW, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                             (int)smem));                                                           \
+            hunt_front_warp_kernel<NW, 16><<<blocks, 32, smem, st>>>(p);                                            \
+        }                                                                                                           \
         break
         switch (nw) {
-            FRONT_REG_CASE(1); FRONT_REG_CASE(2); FRONT_REG_CASE(3); FRONT_REG_CASE(4); FRONT_REG_CASE(5);
-            FRONT_REG_CASE(6);
+            FRONT_WARP_CASE(1); FRONT_WARP_CASE(2); FRONT_WARP_CASE(3); FRONT_WARP_CASE(4); FRONT_WARP_CASE(5);
+            FRONT_WARP_CASE(6); FRONT_WARP_CASE(7); FRONT_WARP_CASE(8);
         default: break;
         }
-#undef FRONT_REG_CASE
+#undef FRONT_WARP_CASE
         c->last_launches++;
         BBB_CUDA(c, cudaGetLastError());
         return BBB_OK;
     }
+    const uint32_t B = 32;
     const bool wide = n > 255;                         // the "no tap" index n must fit the tap type
     const size_t smem = (size_t)B * ((n + 1) * 4 + (size_t)n * 4 * (wide ? 2 : 1));
     const uint32_t blocks = (p.count + B - 1) / B;
@@ -869,7 +938,7 @@ static int launch_front(bbb_ctx *c, const FrontParams &p)
     case NW:                                                                                           \
         BBB_CUDA(c, cudaFuncSetAttribute(hunt_front_kernel<NW, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                          (int)smem));                                                  \
-        hunt_front_kernel<NW, T><<<blocks, B, smem, c->stream>>>(p);                                   \
+        hunt_front_kernel<NW, T><<<blocks, B, smem, st>>>(p);                                          \
         break
     if (!wide) {
         switch (nw) {
@@ -898,10 +967,22 @@ static int check_hunt_n(bbb_ctx *c, uint32_t n)
     return BBB_OK;
 }
 
-extern "C" {
+// p(x) as nwp LSB-first words -> BinaryPolynomial words: coefficient j (of x^(n-j)) at word j/64, bit 63 - j%64
+static void hunt_poly_to_reference(uint32_t n, const uint32_t *p, uint64_t *out, uint32_t *weight)
+{
+    const uint32_t pw64 = (n + 1 + 63) / 64;
+    uint32_t ones = 0;
+    for (uint32_t w = 0; w < pw64; w++) out[w] = 0;
+    for (uint32_t j = 0; j <= n; j++) {
+        const uint32_t i = n - j;
+        if ((p[i >> 5] >> (i & 31)) & 1u) { out[j >> 6] |= 1ull << (63 - (j & 63)); ones++; }
+    }
+    if (weight) *weight = ones;
+}
 
-int bbb_rnghunt_sweep(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uint64_t stride, uint64_t count,
-                      uint32_t k, uint64_t *best, uint32_t *nfound, uint64_t *stage_counts, uint8_t *stage_out)
+static int hunt_sweep(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uint64_t stride, uint64_t count,
+                      uint32_t k, uint64_t *best, uint32_t *nfound, uint64_t *stage_counts, uint8_t *stage_out,
+                      uint64_t *poly_words, uint32_t *weights)
 {
     int rc = check_hunt_n(c, n);
     if (rc) return rc;
@@ -911,43 +992,81 @@ int bbb_rnghunt_sweep(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uin
     c->begin_call();
     c->last_kernel = "rnghunt_sweep";
     const uint32_t nwp = (n + 31) / 32 + 1;
+    const bool want_polys = poly_words || weights;
     const uint64_t batch_max = c->tune_hunt_batch ? c->tune_hunt_batch : (1u << 20);
     const uint32_t cap = (uint32_t)(count < batch_max ? (count ? count : 1) : batch_max);
-    HuntBuffers b;
-    rc = hunt_buffers(c, n, cap, nwp, b);
+    HuntShared sh;
+    HuntSlot slots[2];
+    rc = hunt_setup(c, n, cap, nwp, want_polys, 2, sh, slots);
     if (rc) return rc;
-    BBB_CUDA(c, cudaMemsetAsync(b.counts, 0, 8 * BBB_NSTAGES, c->stream));
-    std::vector<uint64_t> found;
-    std::vector<uint32_t> hit_slots;
-    for (uint64_t done = 0; done < count; done += cap) {
+    // the second stream joins the timed region of the first
+    BBB_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+    BBB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+    std::vector<HuntHit> found;
+    uint32_t turn = 0;
+    for (uint64_t done = 0; done < count; done += cap, turn ^= 1u) {
+        HuntSlot &b = slots[turn];
+        rc = hunt_collect(c, b, stride, nwp, found);          // the batch that used this slot two turns ago
+        if (rc) return rc;
         const uint32_t nb = (uint32_t)(count - done < cap ? count - done : cap);
-        BBB_CUDA(c, cudaMemsetAsync(b.counters, 0, 16, c->stream));
+        BBB_CUDA(c, cudaMemsetAsync(b.counters, 0, 16, b.stream));
         FrontParams p;
         p.n = n; p.seed = seed; p.first = first + done * stride; p.stride = stride; p.count = nb;
         p.out.stage = b.stage; p.out.surv_count = b.counters; p.out.surv_cand = b.surv_cand;
         p.out.surv_poly = b.surv_poly; p.out.poly_out = nullptr; p.dump_taps = nullptr;
-        p.gtaps = n <= 192 ? (uint32_t *)c->scratch(8, (size_t)n * cap * 4) : nullptr;
-        if (n <= 192 && !p.gtaps) return BBB_ECUDA;
-        rc = launch_front(c, p);
+        b.first = p.first;
+        rc = launch_front(c, b.stream, p);
         if (rc) return rc;
-        rc = hunt_back_end(c, n, nb, nwp, b, hit_slots);
+        rc = hunt_back_end(c, n, nb, nwp, sh, b);
         if (rc) return rc;
-        for (uint32_t s : hit_slots) found.push_back(p.first + (uint64_t)s * stride);
         if (stage_out) {
-            BBB_CUDA(c, c->d2h(stage_out + done, b.stage, nb));
-            BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+            BBB_CUDA(c, cudaMemcpyAsync(stage_out + done, b.stage, nb, cudaMemcpyDeviceToHost, b.stream));
+            c->d2h_bytes += nb;
+            BBB_CUDA(c, cudaStreamSynchronize(b.stream));
         }
     }
+    for (uint32_t i = 0; i < 2; i++, turn ^= 1u) {
+        rc = hunt_collect(c, slots[turn], stride, nwp, found);
+        if (rc) return rc;
+    }
+    BBB_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
+    BBB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
     c->end_call();
     unsigned long long counts[BBB_NSTAGES];
-    BBB_CUDA(c, c->d2h(counts, b.counts, sizeof counts));
+    BBB_CUDA(c, c->d2h(counts, sh.counts, sizeof counts));
     BBB_CUDA(c, cudaStreamSynchronize(c->stream));
     if (stage_counts) for (int i = 0; i < BBB_NSTAGES; i++) stage_counts[i] += counts[i];
-    std::sort(found.begin(), found.end());
-    uint32_t nf = (uint32_t)(found.size() < k ? found.size() : k);
-    for (uint32_t i = 0; i < nf; i++) best[i] = found[i];
+    std::sort(found.begin(), found.end(), [](const HuntHit &a, const HuntHit &b) { return a.cand < b.cand; });
+    const uint32_t nf = (uint32_t)(found.size() < k ? found.size() : k);
+    const uint32_t pw64 = (n + 1 + 63) / 64;
+    for (uint32_t i = 0; i < nf; i++) {
+        best[i] = found[i].cand;
+        if (want_polys) {
+            uint64_t tmp[(BBB_MAX_N + 64) / 64 + 1];
+            uint32_t wt = 0;
+            hunt_poly_to_reference(n, found[i].poly.data(), tmp, &wt);
+            if (poly_words) memcpy(poly_words + (size_t)i * pw64, tmp, pw64 * 8);
+            if (weights) weights[i] = wt;
+        }
+    }
     if (nfound) *nfound = nf;
     return BBB_OK;
+}
+
+extern "C" {
+
+int bbb_rnghunt_sweep(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uint64_t stride, uint64_t count,
+                      uint32_t k, uint64_t *best, uint32_t *nfound, uint64_t *stage_counts, uint8_t *stage_out)
+{
+    return hunt_sweep(c, n, seed, first, stride, count, k, best, nfound, stage_counts, stage_out, nullptr, nullptr);
+}
+
+int bbb_rnghunt_sweep_polys(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uint64_t stride, uint64_t count,
+                            uint32_t k, uint64_t *best, uint32_t *nfound, uint64_t *stage_counts,
+                            uint64_t *poly_words, uint32_t *weights)
+{
+    if (c && !poly_words && !weights) return c->fail(BBB_EINVAL, "poly_words and weights are both null");
+    return hunt_sweep(c, n, seed, first, stride, count, k, best, nfound, stage_counts, nullptr, poly_words, weights);
 }
 
 int bbb_rnghunt_candidate(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t cand, uint64_t *matrix_words)
@@ -963,7 +1082,7 @@ int bbb_rnghunt_candidate(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t cand, 
     FrontParams p;
     memset(&p, 0, sizeof p);
     p.n = n; p.seed = seed; p.first = cand; p.stride = 1; p.count = 1; p.dump_taps = d_taps;
-    rc = launch_front(c, p);
+    rc = launch_front(c, c->stream, p);
     if (rc) return rc;
     c->end_call();
     std::vector<uint16_t> taps((size_t)n * 4);
@@ -992,17 +1111,16 @@ int bbb_rnghunt_eval(bbb_ctx *c, uint32_t n, uint64_t ncand, const uint64_t *mat
     const uint32_t nw64 = (n + 63) / 64, nwp = 2 * nw64 + 1, pw64 = (n + 1 + 63) / 64;
     const size_t mat_bytes = (size_t)n * nw64 * 8;
     const uint32_t cap = (uint32_t)(ncand < 65536 ? (ncand ? ncand : 1) : 65536);
-    HuntBuffers b;
-    rc = hunt_buffers(c, n, cap, nwp, b);
+    HuntShared sh;
+    HuntSlot b;
+    rc = hunt_setup(c, n, cap, nwp, false, 1, sh, &b);
     if (rc) return rc;
     uint64_t *d_m = (uint64_t *)c->scratch(5, cap * mat_bytes + (size_t)cap * pw64 * 8);
     if (!d_m) return BBB_ECUDA;
     uint64_t *d_poly = (uint64_t *)((char *)d_m + cap * mat_bytes);
-    std::vector<uint32_t> hit_slots;
     for (uint64_t done = 0; done < ncand; done += cap) {
         const uint32_t nb = (uint32_t)(ncand - done < cap ? ncand - done : cap);
         BBB_CUDA(c, cudaMemsetAsync(b.counters, 0, 16, c->stream));
-        BBB_CUDA(c, cudaMemsetAsync(b.counts, 0, 8 * BBB_NSTAGES, c->stream));
         BBB_CUDA(c, c->h2d(d_m, matrices + done * n * nw64, nb * mat_bytes));
         HuntOut o;
         o.stage = b.stage; o.surv_count = b.counters; o.surv_cand = b.surv_cand; o.surv_poly = b.surv_poly;
@@ -1017,11 +1135,12 @@ int bbb_rnghunt_eval(bbb_ctx *c, uint32_t n, uint64_t ncand, const uint64_t *mat
 #undef DENSE_CASE
         c->last_launches++;
         BBB_CUDA(c, cudaGetLastError());
-        rc = hunt_back_end(c, n, nb, nwp, b, hit_slots);
+        rc = hunt_back_end(c, n, nb, nwp, sh, b);
         if (rc) return rc;
         BBB_CUDA(c, c->d2h(stage + done, b.stage, nb));
         if (poly_words) BBB_CUDA(c, c->d2h(poly_words + done * pw64, d_poly, (size_t)nb * pw64 * 8));
         BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+        b.nb = 0;
     }
     c->end_call();
     return BBB_OK;

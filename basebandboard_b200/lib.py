@@ -96,6 +96,8 @@ SIGNATURES = {
     "bbb_rnghunt_candidate": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, _u64p]),
     "bbb_rnghunt_sweep": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64,
                                     C.c_uint64, C.c_uint32, _u64p, _u32p, _u64p, _u8p]),
+    "bbb_rnghunt_sweep_polys": (C.c_int, [_ctx, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint64,
+                                          C.c_uint64, C.c_uint32, _u64p, _u32p, _u64p, _u64p, _u32p]),
     "bbb_measure_lop3_peak": (C.c_int, [_ctx, _P(C.c_double)]),
 }
 
@@ -385,10 +387,21 @@ class Context:
         self._check(self._L.bbb_rnghunt_candidate(self._h, n, seed, c, _ptr(out, C.c_uint64)))
         return out
 
-    def rnghunt_sweep(self, n, seed, first, count, k=16, stride=1, want_stages=False):
+    def rnghunt_sweep(self, n, seed, first, count, k=16, stride=1, want_stages=False, want_polys=False):
         best = np.zeros(max(k, 1), dtype=np.uint64)
         nfound = C.c_uint32(0)
         counts = np.zeros(5, dtype=np.uint64)
+        if want_polys:
+            pw = (n + 1 + 63) // 64
+            polys = np.zeros(max(k, 1) * pw, dtype=np.uint64)
+            weights = np.zeros(max(k, 1), dtype=np.uint32)
+            self._check(self._L.bbb_rnghunt_sweep_polys(self._h, n, seed, first, stride, count, k,
+                                                        _ptr(best, C.c_uint64), C.byref(nfound),
+                                                        _ptr(counts, C.c_uint64), _ptr(polys, C.c_uint64),
+                                                        _ptr(weights, C.c_uint32)))
+            nf = nfound.value
+            return {"best": [int(b) for b in best[:nf]], "stage_counts": counts,
+                    "polys": polys.reshape(-1, pw)[:nf], "weights": [int(w) for w in weights[:nf]]}
         stages = np.zeros(count, dtype=np.uint8) if want_stages else None
         self._check(self._L.bbb_rnghunt_sweep(self._h, n, seed, first, stride, count, k,
                                               _ptr(best, C.c_uint64), C.byref(nfound),

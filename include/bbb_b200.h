@@ -85,7 +85,8 @@ uint32_t bbb_last_rounds(const bbb_ctx *ctx);
 /* Tuning knobs, for tests and experiments (results never depend on them):
  *   "clt_no_spec" (0/1), "clt_spec_min_steps", "clt_spec_max_blocks",
  *   "prbs_chunk_words", "prbs_stream_reps", "hunt_batch", "hunt_slow_check" (0/1),
- *   "hunt_smem_taps" (0 auto, 1 shared-memory taps, 2 register taps). */
+ *   "hunt_smem_taps" (0 auto, 1 thread-per-candidate kernel with shared-memory taps for every n),
+ *   "hunt_cpw" (candidates per warp pass of the warp-per-candidate kernel: 32 or 16). */
 int  bbb_set_tuning(bbb_ctx *ctx, const char *key, int64_t value);
 /* Region timer: CUDA events on the ctx's stream around any number of calls.
  * bbb_timer_stop waits for the stream and returns the device time in ms. */
@@ -238,6 +239,14 @@ int bbb_rnghunt_candidate(bbb_ctx *ctx, uint32_t n, uint64_t seed, uint64_t c, u
 int bbb_rnghunt_sweep(bbb_ctx *ctx, uint32_t n, uint64_t seed, uint64_t first, uint64_t stride,
                       uint64_t count, uint32_t k, uint64_t *best, uint32_t *nfound,
                       uint64_t *stage_counts, uint8_t *stage_out);
+
+/* The same sweep, also returning what the reference's quality pass looks at (util/verify.py:19-28: the
+ * characteristic polynomial of an accepted matrix): poly_words[i*pw .. ) = the Berlekamp-Massey polynomial
+ * of best[i] as pw = ceil((n+1)/64) MSbit-first words, coefficient 0 = highest power (binary_polynomial.rs:9-11),
+ * weights[i] = its number of terms (103 for the shipped n = 192 matrix).  Either may be NULL, not both. */
+int bbb_rnghunt_sweep_polys(bbb_ctx *ctx, uint32_t n, uint64_t seed, uint64_t first, uint64_t stride,
+                            uint64_t count, uint32_t k, uint64_t *best, uint32_t *nfound,
+                            uint64_t *stage_counts, uint64_t *poly_words, uint32_t *weights);
 
 /* ---- measurement helpers ------------------------------------------------ */
 /* Dependent-free LOP3 issue micro-benchmark: returns thread-instructions/s
