@@ -166,15 +166,37 @@ def test_table_and_shift_add_primitivity_kernels_agree(ctx, n):
     assert fast["stage_counts"][STAGE_ORDER] > 0
 
 
-@pytest.mark.parametrize("n", [16, 33, 100, 192])
-def test_register_and_shared_tap_front_kernels_agree(ctx, n):
-    """hunt_front_reg_kernel (taps in registers, n <= 192) vs hunt_front_kernel (taps in shared memory)."""
-    count = 5000
-    ctx.set_tuning("hunt_smem_taps", 2)       # register kernel for every n <= 192
+@pytest.mark.parametrize("n", [8, 16, 33, 100, 192, 250, 256])
+def test_warp_and_thread_front_kernels_agree(ctx, n):
+    """hunt_front_warp_kernel (one warp per candidate, row masks in registers, n <= 256; both widths of the
+    generation pass) vs hunt_front_kernel (one thread per candidate, byte state + tap lists in shared memory):
+    two independent implementations of binary_matrix.rs:53-76 + berlekamp_massey.rs:5-31."""
+    count = 5000 if n < 250 else 1500
     a = ctx.rnghunt_sweep(n, 21, 7, count, k=8, want_stages=True)
+    ctx.set_tuning("hunt_cpw", 16)
+    a16 = ctx.rnghunt_sweep(n, 21, 7, count, k=8, want_stages=True)
+    ctx.set_tuning("hunt_cpw", 0)
     ctx.set_tuning("hunt_smem_taps", 1)
     try:
         b = ctx.rnghunt_sweep(n, 21, 7, count, k=8, want_stages=True)
     finally:
         ctx.set_tuning("hunt_smem_taps", 0)
     assert np.array_equal(a["stages"], b["stages"]) and a["best"] == b["best"]
+    assert np.array_equal(a16["stages"], b["stages"]) and a16["best"] == b["best"]
+
+
+@pytest.mark.parametrize("n", [16, 64, 192])
+def test_sweep_polys_are_the_oracle_polynomials(ctx, orc, n):
+    """bbb_rnghunt_sweep_polys: the characteristic polynomial of every returned hit, word for word the
+    oracle's Berlekamp-Massey polynomial (berlekamp_massey.rs:5-31), and its weight (util/verify.py:19-28)."""
+    count = 3000 if n < 192 else 20000
+    got = ctx.rnghunt_sweep(n, 1, 0, count, k=64, want_polys=True)
+    plain = ctx.rnghunt_sweep(n, 1, 0, count, k=64)
+    assert got["best"] == plain["best"] and len(got["best"]) > 0
+    assert np.array_equal(got["stage_counts"], plain["stage_counts"])
+    pw = (n + 1 + 63) // 64
+    for c, poly, wt in zip(got["best"], got["polys"], got["weights"]):
+        st, opoly = orc.BinaryMatrix.candidate(n, 1, c).evaluate(want_poly=True)
+        assert st == STAGE_PRIMITIVE
+        assert np.array_equal(poly, opoly[:pw]), c
+        assert wt == sum(bin(int(w)).count("1") for w in opoly[:pw]) and wt % 2 == 1
