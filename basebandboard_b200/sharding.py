@@ -104,12 +104,15 @@ def prbs_detect_sharded(engine, k, nbits, m=0, seed=1, first_bit=0, make_det=Non
     else:
         start = _det_tuple(engine.prbs_spec_state(k, lo, m, seed)) if lo >= 64 else (0, 1, (1 << k) - 1, 0)
     runs = 0
+    ran_from = None
     while True:
-        det = make_det(*start)
-        ctr = engine.prbs_detect(k, cnt, m=m, seed=seed, first_bit=lo, det=det) if cnt else \
-            {"err": 0, "err_valid": 0, "reload_events": 0, "reload_cycles": 0, "injected": 0}
-        runs += 1
-        end = _det_tuple(det) if cnt else start
+        if ran_from != start:                             # only a rank whose start state changed runs again
+            det = make_det(*start)
+            ctr = engine.prbs_detect(k, cnt, m=m, seed=seed, first_bit=lo, det=det) if cnt else \
+                {"err": 0, "err_valid": 0, "reload_events": 0, "reload_cycles": 0, "injected": 0}
+            runs += 1
+            end = _det_tuple(det) if cnt else start
+            ran_from = start
         table = _all_gather_i64(list(start) + list(end))     # [world, 8]
         # the state each rank should have started from: its left neighbour's end state
         wrong = [r for r in range(1, world) if tuple(table[r][:4]) != tuple(table[r - 1][4:])]
@@ -142,9 +145,12 @@ def _loop_sharded(run, spec_state, k, nbits, first_bit, warm_bits=1024):
     else:
         start = run(lo - warm_bits, warm_bits, _det_tuple(spec_state(k, lo - warm_bits)))[1]
     runs = 0
+    ran_from = None
     while True:
-        ctr, end = run(lo, cnt, start) if cnt else (zero, start)
-        runs += 1
+        if ran_from != start:                             # only a rank whose start state changed runs again
+            ctr, end = run(lo, cnt, start) if cnt else (zero, start)
+            runs += 1
+            ran_from = start
         table = _all_gather_i64(list(start) + list(end))     # [world, 8]
         wrong = [r for r in range(1, world) if tuple(table[r][:4]) != tuple(table[r - 1][4:])]
         if not wrong:

@@ -154,6 +154,123 @@ def workload_config(args, world):
     }
 
 
+HUNT_N, HUNT_SEED, HUNT_LOG2, HUNT_K = 192, 1, 24, 16     # BASELINE.json configs[3] as SURVEY.md 8d restates it
+
+
+def hunt_alg_lop3_per_candidate(n):
+    """Algorithmic work of the sweep's dominant kernel (hunt_front_warp_kernel): 2n clocks of x' = A.x
+    (binary_matrix.rs:68-76), each clock = n rows x ceil(n/32) mask words, one LOP3 ((W & M) ^ acc) per word.
+    (The same clocks as sparse gathers: 2n x 31n/8 tap reads -- 286 k at n = 192 -- the form the thread-per-
+    candidate kernel of round 1 used and lost on, shared-memory bound.)"""
+    nw = (n + 31) // 32
+    return 2 * n * nw * 32 * nw
+
+
+def crc_u64(words):
+    import zlib
+    import numpy as np
+    return zlib.crc32(np.ascontiguousarray(words, dtype=np.uint64).tobytes()) & 0xFFFFFFFF
+
+
+def cpu_rnghunt_rate(seconds, threads):
+    """Oracle port of the rnghunt worker loop (oracle/rnghunt_ref.c) on `threads` host threads: candidates/s
+    on a bounded prefix of the same candidate stream."""
+    from oracle import oracle
+    t0 = time.perf_counter()
+    oracle.rnghunt_sweep(HUNT_N, HUNT_SEED, 0, 64 * threads, threads=threads)
+    cal = 64 * threads / (time.perf_counter() - t0)
+    cnt = max(64 * threads, int(cal * seconds))
+    t0 = time.perf_counter()
+    _, counts = oracle.rnghunt_sweep(HUNT_N, HUNT_SEED, 0, cnt, threads=threads)
+    return cnt / (time.perf_counter() - t0), cnt, [int(v) for v in counts]
+
+
+def python_loop_rate(nsamp=4000):
+    """The reference's literal implementation, clt-grng-evaluate.py:8-16, restated in oracle/oracle.py
+    (py_clt_evaluate_loop): samples/s on one core."""
+    from oracle import oracle
+    t0 = time.perf_counter()
+    oracle.py_clt_evaluate_loop(nsamp)
+    return nsamp / (time.perf_counter() - t0)
+
+
+def run_rnghunt_leg(args, ctx, rank, world, local_rank, lop3_peak, barrier):
+    """The metric's second half (BASELINE.json: "rnghunt candidates/s at 1/2/4/8 B200", configs[3]): n = 192,
+    seed 1, the FIXED candidate set [0, 2^24) interleaved c = rank (mod N) (strong scaling), per-rank best-16
+    all-gathered and merged inside the timed region (rnghunt.rs:14,23-57).  Returns the dict that goes under
+    "secondary": {"rnghunt": ...} of the JSON line (rank 0), None elsewhere."""
+    import torch
+    import torch.distributed as dist
+    from basebandboard_b200 import sharding
+    total = 1 << args.hunt_log2
+    res = {}
+
+    def step():
+        res["r"] = sharding.rnghunt_sweep_sharded(ctx, HUNT_N, HUNT_SEED, 0, total, k=HUNT_K)
+        return ctx.last_launches
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(physical_gpu_index(local_rank))
+    sampler.start()
+    launches = 0
+    t0 = time.perf_counter()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        launches += step()
+    dev_ms = ctx.timer_stop()
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.finish()
+    h2d, d2h = ctx.last_h2d_bytes, ctx.last_d2h_bytes
+    sweep_ms = ctx.last_device_ms                    # this rank's share of the sweep, device-timed, one call
+    barrier()
+    # e2e: the same public call, host arguments in, merged host ranking out, wall clock
+    t1 = time.perf_counter()
+    step()
+    e2e_ms = (time.perf_counter() - t1) * 1e3
+    t = torch.tensor([dev_ms, wall_ms, e2e_ms, sweep_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms, e2e_ms, sweep_ms = [float(v) for v in t.cpu()]
+    if rank != 0:
+        return None
+    value = total * args.steps / (dev_ms * 1e-3)
+    alg = hunt_alg_lop3_per_candidate(HUNT_N)
+    per_gpu = (total / world) / (sweep_ms * 1e-3)
+    ach = per_gpu * alg / 1e12
+    out = {
+        "metric": "rnghunt_candidates_per_s", "value": value, "unit": "candidates/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+        "scaling": "strong", "dtype": "u32 GF(2)",
+        "config": {"workload": "rnghunt sweep n=%d, seed %d, fixed candidate set [0, 2^%d) interleaved c = rank (mod N), "
+                               "merged best-%d (BASELINE.json configs[3])" % (HUNT_N, HUNT_SEED, args.hunt_log2, HUNT_K),
+                   "collective": "all-gather of k indices + all-reduce of 5 stage counts, inside the timed region"
+                                 if world > 1 else "none"},
+        "wall_ms_per_step": wall_ms / args.steps, "clocks": clocks,
+        "e2e": {"value": total / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "api": "bbb_rnghunt_sweep per rank + merge (host scalars in, host ranking out)"},
+        "gpu_launches": launches,
+        "roofline": {"bound": "alu", "kernel": "hunt_front_warp", "achieved": ach, "peak": lop3_peak / 1e12,
+                     "unit": "T thread-instr/s (LOP3-equivalent)", "frac": ach / (lop3_peak / 1e12), "traffic": None,
+                     "launch_ms_per_2p20": sweep_ms / max(1.0, total / world / (1 << 20)),
+                     "note": "algorithmic work = 2n clocks x n rows x ceil(n/32) mask words, one LOP3 each = %d "
+                             "thread-instr per candidate (binary_matrix.rs:68-76); parity, ballots, candidate "
+                             "generation, Berlekamp-Massey and the primitivity stage are not counted; peak = LOP3 "
+                             "issue rate measured live (bbb_measure_lop3_peak); HBM traffic ~0" % alg},
+        "result_check": {"best": [int(b) for b in res["r"]["best"]],
+                         "stage_counts": [int(v) for v in res["r"]["stage_counts"]]},
+    }
+    if not args.no_cpu_baseline:
+        cores = host_cores()
+        rate, cnt, counts = cpu_rnghunt_rate(min(args.cpu_seconds, 8.0), cores)
+        out["cpu_baseline"] = {"value": rate, "unit": "candidates/s", "cores": cores, "kind": "port",
+                               "sample": "candidates [0, %d) of the same stream (oracle/rnghunt_ref.c, %d threads), "
+                                         "stage counts %s" % (cnt, cores, counts)}
+    return out
+
+
 def run_secondary(args, ctx, rank, world, local_rank):
     """The other BASELINE.json configs through the same contract (device-timed value, e2e through the
     host-buffer API, max over ranks, clocks).  One JSON line from rank 0."""
@@ -190,38 +307,32 @@ def run_secondary(args, ctx, rank, world, local_rank):
         dtype = "u64 (GF(2) word recurrence)"
         l2 = "output (%d MiB) exceeds L2; nothing is read" % (nbits >> 23)
     elif w == "prbs_detect":
+        # rank r owns bits [r*2^b, (r+1)*2^b); the detector state is handed from rank to rank (speculate the locked
+        # state, all-gather end states, re-run on mismatch) and the 5 counters are all-reduced -- all inside step()
         nbits = 1 << args.log2_bits
-        first = rank * nbits
         def step():
-            det = lib.DetState(*((0, 1, (1 << args.k) - 1, 0) if rank == 0 else
-                                 sharding._det_tuple(lib.prbs_spec_state(args.k, first, args.err_m, 1))))
-            extra["ctr"] = ctx.prbs_detect(args.k, nbits, m=args.err_m, seed=1, first_bit=first, det=det)
-            extra["rounds"] = ctx.last_rounds
-            return ctx.last_launches
+            ctr, final, runs = sharding.prbs_detect_sharded(ctx, args.k, world * nbits, m=args.err_m, seed=1)
+            extra["ctr"], extra["rounds"], extra["runs"], extra["final"] = ctr, ctx.last_rounds, runs, final
+            return ctx.last_launches * runs
         def step_e2e():
             step()
             return nbits, ctx.last_h2d_bytes + 16, ctx.last_d2h_bytes
         units, metric, unit, scale = nbits, "prbs_detect_tbit_per_s", "Tbit/s", 1e-12
-        workload = ("PRBS-%d generate + Bernoulli(2^-%d) channel + self-synchronising error count, 2^%d bits/GPU "
-                    "(BASELINE.json configs[1])" % (args.k, args.err_m, args.log2_bits))
+        workload = ("PRBS-%d generate + Bernoulli(2^-%d) channel + self-synchronising error count, 2^%d bits/GPU, "
+                    "contiguous bit ranges with detector-state hand-off (BASELINE.json configs[1])"
+                    % (args.k, args.err_m, args.log2_bits))
         dtype = "u32/u64 integer"
         l2 = "no HBM-resident input"
     elif w == "prbs_slicer":
-        # SURVEY 8f-1 composite; rank r owns bits [r*2^b, (r+1)*2^b) (PRBS and noise are indexed by absolute bit) and
-        # starts from the detector state a 1024-bit warm-up window leaves (sharding._loop_sharded's speculation)
+        # SURVEY 8f-1 composite; contiguous bit ranges per rank (PRBS and noise are indexed by absolute bit), start
+        # state speculated from a 1024-bit warm-up window, hand-off loop and counter all-reduce inside step()
         nbits = 1 << args.log2_bits
-        first = rank * nbits
         ctx.lutopt_load_shipped(N_STATE)
         def step():
-            det = lib.DetState(0, 1, (1 << args.k) - 1, 0)
-            if rank:
-                det = lib.DetState(*sharding._det_tuple(lib.prbs_spec_state(args.k, first - 1024, 0, 1)))
-                ctx.prbs_slicer_detect(args.k, 1024, init=1, amplitude=args.amplitude, noise_var=args.noise_var,
-                                       spb=args.spb, delay=0, first_bit=first - 1024, det=det)
-            extra["ctr"] = ctx.prbs_slicer_detect(args.k, nbits, init=1, amplitude=args.amplitude, noise_var=args.noise_var,
-                                                  spb=args.spb, delay=0, first_bit=first, det=det)
-            extra["rounds"] = ctx.last_rounds
-            return ctx.last_launches
+            ctr, final, runs = sharding.prbs_slicer_detect_sharded(ctx, args.k, world * nbits, init=1, amplitude=args.amplitude,
+                                                                   noise_var=args.noise_var, spb=args.spb, delay=0)
+            extra["ctr"], extra["rounds"], extra["runs"], extra["final"] = ctr, ctx.last_rounds, runs, final
+            return ctx.last_launches * runs
         def step_e2e():
             step()
             return nbits, ctx.last_h2d_bytes + 48, ctx.last_d2h_bytes
@@ -235,19 +346,13 @@ def run_secondary(args, ctx, rank, world, local_rank):
         # SURVEY 8f-3 composite: shaped TX word + noise -> slicer at sample `delay` -> detector; ranks as for prbs_slicer
         from basebandboard_b200 import shaper
         nbits = 1 << args.log2_bits
-        first = rank * nbits
         ctx.lutopt_load_shipped(N_STATE)
         coeff = shaper.tx_sets()[16]
         def step():
-            det = lib.DetState(0, 1, (1 << args.k) - 1, 0)
-            if rank:
-                det = lib.DetState(*sharding._det_tuple(lib.prbs_spec_state(args.k, first - 1024, 0, 1)))
-                ctx.prbs_shaped_slicer_detect(args.k, 1024, coeff, init=1, noise_var=args.noise_var, delay=4,
-                                              first_bit=first - 1024, det=det)
-            extra["ctr"] = ctx.prbs_shaped_slicer_detect(args.k, nbits, coeff, init=1, noise_var=args.noise_var, delay=4,
-                                                         first_bit=first, det=det)
-            extra["rounds"] = ctx.last_rounds
-            return ctx.last_launches
+            ctr, final, runs = sharding.prbs_shaped_slicer_detect_sharded(ctx, args.k, world * nbits, coeff, init=1,
+                                                                          noise_var=args.noise_var, delay=4)
+            extra["ctr"], extra["rounds"], extra["runs"], extra["final"] = ctr, ctx.last_rounds, runs, final
+            return ctx.last_launches * runs
         def step_e2e():
             step()
             return nbits, ctx.last_h2d_bytes + 48 + 128, ctx.last_d2h_bytes
@@ -315,12 +420,14 @@ def run_secondary(args, ctx, rank, world, local_rank):
     sampler = ClockSampler(physical_gpu_index(local_rank))
     sampler.start()
     launches = 0
-    dev_ms = 0.0
+    kernel_ms = 0.0
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    ctx.timer_start()                       # CUDA events on the library's stream around the K steps: host-side hand-off
+    for _ in range(args.steps):             # and the small collectives of the sharded legs are inside
         launches += step()
         ctx.sync()
-        dev_ms += ctx.last_device_ms
+        kernel_ms += ctx.last_device_ms
+    dev_ms = ctx.timer_stop()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.finish()
     barrier()
@@ -382,14 +489,15 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                         "shared-memory pipe is the busier one (82 % of its wavefront peak, ALU 75 %), "
                                         "profiles/r1_dec_kernels_ncu_full.txt"}
         if "ctr" in extra:
-            line["result_check"] = dict(extra["ctr"], rounds=extra["rounds"])
+            line["result_check"] = dict(extra["ctr"], rounds=extra["rounds"], runs=extra["runs"],
+                                        final_state=list(extra["final"]), counters="all-reduced over the ranks")
         if w == "rnghunt":
             # dominant kernel hunt_front: one shared-memory gather per tap per clock (2n clocks per candidate)
             from basebandboard_b200 import recurrences as _rec
             n_ = args.hunt_n
             taps_per_cand = 2.0 * n_ * (n_ * 31.0 / 8.0)          # row weights [3,4,4,4,4,4,4,4]: 31/8 taps per row
             sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
-            lsu_peak = sm * 32 * clocks.get("sm_mhz", 1965) * 1e6 / 1e12
+            lsu_peak = sm * 32 * (clocks.get("sm_mhz") or 1965) * 1e6 / 1e12
             ach = value / world * taps_per_cand / 1e12
             line["roofline"] = {"bound": "lsu", "kernel": "hunt_front", "achieved": ach, "peak": lsu_peak,
                                 "unit": "T shared-memory lane-loads/s", "frac": ach / lsu_peak, "traffic": None,
@@ -452,6 +560,9 @@ def main():
     ap.add_argument("--noise-var-stream", type=int, default=-1, help="clt_stream: >= 0 stores int16 g*noise_var")
     ap.add_argument("--hunt-n", type=int, default=192)
     ap.add_argument("--log2-candidates", type=int, default=20, help="rnghunt candidates per GPU per step")
+    ap.add_argument("--hunt-log2", type=int, default=HUNT_LOG2,
+                    help="default line, secondary.rnghunt: log2 of the fixed candidate set shared by all ranks")
+    ap.add_argument("--no-secondary", action="store_true", help="default line without the rnghunt leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample length")
     ap.add_argument("--ref-step-seconds", type=float, default=4.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -509,6 +620,7 @@ def main():
         return launches
 
     lop3_peak = max(ctx.measure_lop3_peak() for _ in range(3))
+    sm_count = torch.cuda.get_device_properties(local_rank).multi_processor_count
 
     for _ in range(args.warmup):
         step_device()
@@ -535,6 +647,11 @@ def main():
     one_call_ms = ctx.last_device_ms
     kernel_name = ctx.last_kernel
     hist_dev = acc.cpu().numpy().astype("uint64")
+    # the reduced result of one step, read back: every rank's shard must be in it
+    if world > 1:
+        dist.all_reduce(acc)
+    acc_all = acc.cpu().numpy().astype("uint64")
+    assert int(acc_all[:N_STATE + 1].sum()) == world * count, "all-reduced histogram does not hold world * count samples"
 
     # e2e: host buffers through bbb_clt_hist, copies inside the timed region
     e2e_steps = max(1, min(args.steps, 2))
@@ -572,15 +689,21 @@ def main():
             "gpu_launches": launches,
             "roofline": {"bound": "alu", "kernel": kernel_name, "achieved": achieved / 1e12, "peak": lop3_peak / 1e12,
                          "unit": "T thread-instr/s (LOP3-equivalent)", "frac": achieved / lop3_peak,
-                         "traffic": 38887680 if kernel_name == "clt256_fused2" else None,
-                         "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one clt256_hist2_kernel launch "
-                                         "(ncu --set full, profiles/r1_clt256_fused2_ncu_full.txt): the 256 seed planes "
-                                         "x 37888 threads x 4 B, read once per launch whatever the sample count; 0 B written",
+                         "traffic": 38887680 if (kernel_name == "clt256_fused2" and not args.tune and sm_count == 148) else None,
+                         "traffic_note": "NOT re-measured in this run: dram__bytes_read.sum + dram__bytes_write.sum of one "
+                                         "clt256_hist2_kernel launch at this geometry (148 SMs x 2 CTAs x 128 threads, default "
+                                         "tuning; ncu --set full, profiles/r1_clt256_fused2_ncu_full.txt) = the 256 seed planes "
+                                         "x 37888 threads x 4 B, read once per launch whatever the sample count; 0 B written; "
+                                         "null under --tune or another SM count",
                          "launch_ms": one_call_ms,
                          "note": "integer-pipe bound, not HBM/tensor: algorithmic work = 986 LOP3 per 32 "
                                  "samples (492 recurrence + 494 popcount tree); peak = LOP3 issue rate measured "
                                  "live on this GPU (bbb_measure_lop3_peak); HBM traffic ~0 B/sample"},
-            "result_check": {"hist_total": int(h.sum()), "sum": int(s1), "sumsq": int(s2)},
+            "result_check": {"hist_total": int(h.sum()), "sum": int(s1), "sumsq": int(s2),
+                             "reduced_hist_total": int(acc_all[:N_STATE + 1].sum()), "reduced_expected": world * count,
+                             "reduced_sum": int(acc_all[N_STATE + 1:N_STATE + 2].view("int64")[0]),
+                             "reduced_sumsq": int(acc_all[N_STATE + 2]),
+                             "reduced_crc32_u64x259": crc_u64(acc_all)},
         }
         if not args.no_cpu_baseline:
             cores = host_cores()
@@ -588,7 +711,16 @@ def main():
             n_cpu = max(1 << 21, int(cal * args.cpu_seconds))
             rate = cpu_port_rate(n_cpu, cores)
             line["cpu_baseline"] = {"value": rate / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
-                                    "sample": "first %d samples of the workload (oracle/gen.c, %d threads)" % (n_cpu, cores)}
+                                    "sample": "first %d samples of the workload (oracle/gen.c, %d threads)" % (n_cpu, cores),
+                                    "python_loop": {"value": python_loop_rate() / 1e9, "unit": UNIT, "cores": 1,
+                                                    "sample": "4000 samples through the reference's literal loop, "
+                                                              "clt-grng-evaluate.py:8-16 (numpy scalar subtractions)"}}
+    if not args.no_secondary:
+        hunt = run_rnghunt_leg(args, ctx, rank, world, local_rank, lop3_peak, barrier)
+        if rank == 0:
+            line["secondary"] = {"rnghunt": hunt}
+            line["gpu_launches_secondary"] = hunt["gpu_launches"]
+    if rank == 0:
         emit_json(line)
     ctx.close()
     if world > 1:

@@ -550,6 +550,25 @@ def np_clt(n, x_int):
     return int(x[0])
 
 
+def py_clt_evaluate_loop(nsamp, n=256, seed=None):
+    """clt-grng-evaluate.py:4-16 restated literally (the reference's own implementation of the CLT tree:
+    255 scalar numpy subtractions per sample on random bits).  Returns the int16 samples; bench.py times it
+    once as cpu_baseline.python_loop."""
+    logn = int(np.log2(n))
+    rng = np.random.RandomState(seed)
+    samples = np.empty(nsamp, dtype=np.int16)
+    for sampidx in range(nsamp):
+        x = rng.randint(2, size=n).astype(np.int16)
+        for level in range(logn):
+            level_n = 2 ** (logn - level)
+            y = np.zeros(level_n // 2, dtype=np.int16)
+            for pair in range(0, level_n, 2):
+                y[pair // 2] = x[pair] - x[pair + 1]
+            x = y
+        samples[sampidx] = x[0]
+    return samples
+
+
 def py_prbs_bits(k, nbits, lfsr=1):
     """prbs.py:112-113."""
     taps = {7: 6, 9: 5, 11: 9, 15: 14, 20: 3, 23: 18, 31: 28}
