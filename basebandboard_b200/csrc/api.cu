@@ -1,6 +1,7 @@
 // api.cu -- context management, host-side GF(2) jump-ahead operators, LUTOPT
 // loading, derived statistics and the LOP3 roofline micro-benchmark.
 #include <cmath>
+#include <thread>
 
 #include "bbb_internal.h"
 #include "recurrences_data.inc"
@@ -151,6 +152,75 @@ void bbb_ctx::power(uint64_t e, HostMat &out)
     out = std::move(acc);
 }
 
+// ---------------------------------------------------------------------------
+// chunked, double-buffered delivery of a materialised stream to pageable host memory
+// ---------------------------------------------------------------------------
+static void host_copy_parallel(char *dst, const char *src, size_t bytes, uint32_t threads)
+{
+    if (threads <= 1 || bytes < (8u << 20)) { memcpy(dst, src, bytes); return; }
+    const size_t per = ((bytes + threads - 1) / threads + 4095) & ~(size_t)4095;
+    std::vector<std::thread> pool;
+    for (uint32_t t = 1; t < threads; t++) {
+        const size_t lo = (size_t)t * per;
+        if (lo >= bytes) break;
+        const size_t len = bytes - lo < per ? bytes - lo : per;
+        pool.emplace_back([=] { memcpy(dst + lo, src + lo, len); });
+    }
+    memcpy(dst, src, bytes < per ? bytes : per);
+    for (auto &th : pool) th.join();
+}
+
+int bbb_stream_to_host(bbb_ctx *c, int dev_slot, void *out, size_t total, size_t align, size_t chunk_default,
+                       const std::function<int(size_t off, size_t bytes, void *dev)> &gen)
+{
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    if (!align) align = 1;
+    size_t chunk = c->tune_stream_chunk ? (size_t)c->tune_stream_chunk : chunk_default;
+    chunk = chunk / align * align;
+    if (chunk < align) chunk = align;
+    if (chunk > total) chunk = (total + align - 1) / align * align;
+    if (!chunk) chunk = align;
+    const size_t slot_bytes = (chunk + 255) & ~(size_t)255;
+    uint32_t threads = c->tune_host_copy_threads;
+    if (!threads) {
+        threads = std::thread::hardware_concurrency();
+        threads = threads > 8 ? 8 : (threads ? threads : 1);
+    }
+    c->begin_call();
+    struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
+    char *d = (char *)c->scratch(dev_slot, 2 * slot_bytes);
+    char *h = (char *)c->pinned(1, 2 * slot_bytes);
+    if (!d || !h) return BBB_ECUDA;
+    const size_t nchunks = (total + chunk - 1) / chunk;
+    auto drain = [&](size_t i) -> int {
+        const int slot = (int)(i & 1);
+        const size_t off = i * chunk, bytes = total - off < chunk ? total - off : chunk;
+        BBB_CUDA(c, cudaEventSynchronize(c->ev_slot[slot]));
+        host_copy_parallel((char *)out + off, h + slot * slot_bytes, bytes, threads);
+        return BBB_OK;
+    };
+    for (size_t i = 0; i < nchunks; i++) {
+        const int slot = (int)(i & 1);
+        const size_t off = i * chunk, bytes = total - off < chunk ? total - off : chunk;
+        int rc = gen(off, bytes, d + slot * slot_bytes);             // kernels of chunk i on c->stream
+        if (rc) return rc;
+        BBB_CUDA(c, cudaEventRecord(c->ev_aux[slot], c->stream));
+        BBB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_aux[slot], 0));
+        BBB_CUDA(c, cudaMemcpyAsync(h + slot * slot_bytes, d + slot * slot_bytes, bytes, cudaMemcpyDeviceToHost, c->stream2));
+        c->d2h_bytes += bytes;
+        BBB_CUDA(c, cudaEventRecord(c->ev_slot[slot], c->stream2));
+        if (i) { rc = drain(i - 1); if (rc) return rc; }             // chunk i-1 leaves the staging buffer meanwhile
+    }
+    if (nchunks) { int rc = drain(nchunks - 1); if (rc) return rc; }
+    BBB_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
+    BBB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+    c->nest--;          // close the outer timing region (the guard's decrement is balanced below)
+    c->end_call();
+    c->nest++;
+    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return BBB_OK;
+}
+
 extern "C" {
 
 int bbb_version(void) { return 100; }
@@ -176,6 +246,8 @@ int bbb_create(int device, bbb_ctx **out)
         cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_slot[0], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_slot[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_aux[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_aux[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
         cudaEventCreate(&c->evt0) != cudaSuccess || cudaEventCreate(&c->evt1) != cudaSuccess) {
         delete c;
@@ -196,6 +268,7 @@ void bbb_destroy(bbb_ctx *c)
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
     for (int i = 0; i < 2; i++) if (c->ev_slot[i]) cudaEventDestroy(c->ev_slot[i]);
+    for (int i = 0; i < 2; i++) if (c->ev_aux[i]) cudaEventDestroy(c->ev_aux[i]);
     if (c->stream2) cudaStreamDestroy(c->stream2);
     if (c->d_row_ptr) cudaFree(c->d_row_ptr);
     if (c->d_taps) cudaFree(c->d_taps);
@@ -241,6 +314,8 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
     else if (!strcmp(key, "hunt_smem_taps")) c->tune_hunt_smem_taps = (int)value;
     else if (!strcmp(key, "hunt_slow_check")) c->tune_hunt_slow_check = value != 0;
     else if (!strcmp(key, "hunt_batch")) c->tune_hunt_batch = value < 0 ? 0u : (uint32_t)value;
+    else if (!strcmp(key, "stream_chunk_bytes")) c->tune_stream_chunk = value < 0 ? 0ull : (uint64_t)value;
+    else if (!strcmp(key, "host_copy_threads")) c->tune_host_copy_threads = value < 0 ? 0u : (uint32_t)value;
     else if (!strcmp(key, "hunt_cpw")) c->tune_hunt_cpw = value == 16 ? 16u : 0u;
     else if (!strcmp(key, "prbs_stream_reps")) c->tune_prbs_stream_reps = value < 0 ? 0u : (uint32_t)value;
     else return c->fail(BBB_EINVAL, "unknown tuning key %s", key);

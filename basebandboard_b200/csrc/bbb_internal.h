@@ -7,6 +7,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -37,7 +38,7 @@ struct bbb_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;    // second queue: overlapped batches (rnghunt) and chunked D2H copies (streams)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evt0 = nullptr, evt1 = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_slot[2] = {nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_slot[2] = {nullptr, nullptr}, ev_aux[2] = {nullptr, nullptr};
     uint64_t h2d_bytes = 0, d2h_bytes = 0;
     int sm_count = 0;
     std::string err;
@@ -63,6 +64,8 @@ struct bbb_ctx {
     int tune_hunt_smem_taps = 0;        // 1: never use the taps-in-registers front kernel
     int tune_hunt_slow_check = 0;       // 1: always use the shift-and-add primitivity kernel
     uint32_t tune_hunt_batch = 0;       // 0: 2^20 candidates per rnghunt batch
+    uint64_t tune_stream_chunk = 0;     // bytes per chunk of the host-buffer stream calls (0: 64 MiB / 256 MiB)
+    uint32_t tune_host_copy_threads = 0; // threads copying a chunk out of the pinned staging buffer (0: up to 8)
     uint32_t tune_hunt_cpw = 0;         // candidates per warp pass of hunt_front_warp_kernel: 0/32, or 16
     uint32_t last_rounds = 0;           // kernel rounds of the last bbb_prbs_detect
     // PRBS jump tables per k (prbs.cu), built on first use
@@ -115,6 +118,14 @@ struct bbb_ctx {
         cudaError_t e__ = (call);                                 \
         if (e__ != cudaSuccess) return (ctx)->cuda_fail(e__, #call); \
     } while (0)
+
+// api.cu: a materialised stream delivered to caller-owned (pageable) host memory.  `gen(off, bytes, dev)` queues
+// the kernels that write bytes [off, off+bytes) of the stream to `dev` on ctx->stream; chunks alternate between
+// two device buffers (scratch slot `dev_slot`) and two pinned staging buffers, the D2H copy of chunk i runs on
+// ctx->stream2 beside the kernels of chunk i+1, and the host thread(s) copy chunk i-1 out of the staging buffer
+// meanwhile.  One timing region (bbb_last_device_ms) spans the call.  `align`: chunk boundaries in bytes.
+int bbb_stream_to_host(bbb_ctx *ctx, int dev_slot, void *out, size_t total_bytes, size_t align, size_t chunk_default,
+                       const std::function<int(size_t off, size_t bytes, void *dev)> &gen);
 
 // prbs.cu
 void bbb_prbs_free_tables(bbb_ctx *ctx);

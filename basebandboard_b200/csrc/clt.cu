@@ -623,15 +623,13 @@ int bbb_clt_stream(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t coun
     if (rc) return rc;
     if ((out8 != nullptr) == (out16 != nullptr))
         return c->fail(BBB_EINVAL, "exactly one of out8/out16 must be given");
-    const size_t bytes = (size_t)count * (out8 ? 1 : 2);
-    void *d = c->scratch(4, bytes ? bytes : 1);
-    if (!d) return BBB_ECUDA;
-    rc = bbb_clt_stream_dev(c, x0, first, count, model, noise_var, out8 ? (int8_t *)d : nullptr,
-                            out16 ? (int16_t *)d : nullptr);
-    if (rc) return rc;
-    BBB_CUDA(c, c->d2h(out8 ? (void *)out8 : (void *)out16, d, bytes));
-    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return BBB_OK;
+    const size_t eb = out8 ? 1 : 2;
+    // 2^28-byte chunks: each chunk re-seeds its streams by jump-ahead, which must stay small beside the chunk
+    return bbb_stream_to_host(c, 4, out8 ? (void *)out8 : (void *)out16, (size_t)count * eb, 65536, (size_t)256 << 20,
+                              [&](size_t off, size_t bytes, void *dev) {
+                                  return bbb_clt_stream_dev(c, x0, first + off / eb, bytes / eb, model, noise_var,
+                                                            out8 ? (int8_t *)dev : nullptr, out16 ? (int16_t *)dev : nullptr);
+                              });
 }
 
 int bbb_clt_stream_dec_dev(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t spb, uint32_t delay,
@@ -655,13 +653,11 @@ int bbb_clt_stream_dec(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
     int rc = check_loaded(c, x0);
     if (rc) return rc;
     if (!out8) return c->fail(BBB_EINVAL, "out is null");
-    void *d = c->scratch(4, count ? (size_t)count : 1);
-    if (!d) return BBB_ECUDA;
-    rc = bbb_clt_stream_dec_dev(c, x0, first, count, spb, delay, (int8_t *)d);
-    if (rc) return rc;
-    BBB_CUDA(c, c->d2h(out8, d, (size_t)count));
-    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return BBB_OK;
+    return bbb_stream_to_host(c, 4, out8, (size_t)count, 65536, (size_t)256 << 20,
+                              [&](size_t off, size_t bytes, void *dev) {
+                                  return bbb_clt_stream_dec_dev(c, x0, first + (uint64_t)off * spb, bytes, spb, delay,
+                                                                (int8_t *)dev);
+                              });
 }
 
 int bbb_lutopt_stream_dev(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count,
@@ -682,14 +678,12 @@ int bbb_lutopt_stream(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t c
     int rc = check_loaded(c, x0);
     if (rc) return rc;
     if (!out_words) return c->fail(BBB_EINVAL, "out is null");
-    const size_t bytes = (size_t)count * ((c->n + 63) / 64) * 8;
-    void *d = c->scratch(4, bytes ? bytes : 1);
-    if (!d) return BBB_ECUDA;
-    rc = bbb_lutopt_stream_dev(c, x0, first, count, (uint64_t *)d);
-    if (rc) return rc;
-    BBB_CUDA(c, c->d2h(out_words, d, bytes));
-    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return BBB_OK;
+    const size_t step_bytes = (size_t)((c->n + 63) / 64) * 8;
+    return bbb_stream_to_host(c, 4, out_words, (size_t)count * step_bytes, step_bytes * 4096, (size_t)256 << 20,
+                              [&](size_t off, size_t bytes, void *dev) {
+                                  return bbb_lutopt_stream_dev(c, x0, first + off / step_bytes, bytes / step_bytes,
+                                                               (uint64_t *)dev);
+                              });
 }
 
 }  // extern "C"

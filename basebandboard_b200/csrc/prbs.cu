@@ -501,15 +501,13 @@ int bbb_prbs_stream(bbb_ctx *c, uint32_t k, uint32_t state0, uint64_t first_bit,
 {
     int rc = check_prbs_args(c, k, state0);
     if (rc) return rc;
+    if (nbits % 64) return c->fail(BBB_EINVAL, "nbits must be a multiple of 64");
     if (!out_words && nbits) return c->fail(BBB_EINVAL, "out is null");
-    const size_t bytes = (size_t)(nbits / 64) * 8;
-    void *d = c->scratch(4, bytes ? bytes : 1);
-    if (!d) return BBB_ECUDA;
-    rc = bbb_prbs_stream_dev(c, k, state0, first_bit, nbits, (uint64_t *)d);
-    if (rc) return rc;
-    if (bytes) BBB_CUDA(c, c->d2h(out_words, d, bytes));
-    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return BBB_OK;
+    return bbb_stream_to_host(c, 4, out_words, (size_t)(nbits / 8), 8 * 4096, (size_t)64 << 20,
+                              [&](size_t off, size_t bytes, void *dev) {
+                                  return bbb_prbs_stream_dev(c, k, state0, first_bit + (uint64_t)off * 8,
+                                                             (uint64_t)bytes * 8, (uint64_t *)dev);
+                              });
 }
 
 // splitmix64-keyed channel, host copy (bbb_prbs_spec_state only)
@@ -1095,14 +1093,11 @@ int bbb_tx_stream(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, co
 {
     if (!c) return BBB_EINVAL;
     if (!out) return c->fail(BBB_EINVAL, "out is null");
-    BBB_CUDA(c, cudaSetDevice(c->device));
-    int16_t *d = (int16_t *)c->scratch(12, (size_t)nbits * 16 + 16);
-    if (!d) return BBB_ECUDA;
-    int rc = bbb_tx_stream_dev(c, k, first_bit, nbits, coeff, bit_en, x0, noise_var, d);
-    if (rc) return rc;
-    BBB_CUDA(c, c->d2h(out, d, (size_t)nbits * 16));
-    BBB_CUDA(c, cudaStreamSynchronize(c->stream));
-    return BBB_OK;
+    return bbb_stream_to_host(c, 12, out, (size_t)nbits * 16, 16 * 4096, (size_t)(x0 ? 256 : 64) << 20,
+                              [&](size_t off, size_t bytes, void *dev) {
+                                  return bbb_tx_stream_dev(c, k, first_bit + off / 16, bytes / 16, coeff, bit_en, x0,
+                                                           noise_var, (int16_t *)dev);
+                              });
 }
 
 int bbb_prbs_shaped_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff,

@@ -145,6 +145,12 @@ def _ptr(a, typ):
     return a.ctypes.data_as(_P(typ))
 
 
+def _check_out(out, dtype, size):
+    if not (isinstance(out, np.ndarray) and out.dtype == dtype and out.size == size and out.flags.c_contiguous):
+        raise ValueError("out must be a C-contiguous %s array of %d elements" % (np.dtype(dtype).name, size))
+    return out
+
+
 class Context:
     """One per GPU per host thread (the `bbb_ctx*` of the C ABI)."""
 
@@ -238,9 +244,10 @@ class Context:
         self._check(self._L.bbb_lutopt_jump(self._h, _ptr(xin, C.c_uint64), e, _ptr(out, C.c_uint64)))
         return state_int(out)
 
-    def lutopt_stream(self, init, first, count):
+    def lutopt_stream(self, init, first, count, out=None):
+        """`out`: caller-owned uint64 array of count * ceil(n/64) words to fill (reused across calls)."""
         nw = (self.n + 63) // 64
-        out = np.zeros(count * nw, dtype=np.uint64)
+        out = np.zeros(count * nw, dtype=np.uint64) if out is None else _check_out(out, np.uint64, count * nw)
         x0 = state_words(init, self.n)
         self._check(self._L.bbb_lutopt_stream(self._h, _ptr(x0, C.c_uint64), first, count,
                                               _ptr(out, C.c_uint64)))
@@ -267,14 +274,14 @@ class Context:
         self._check(self._L.bbb_clt_hist_dev(self._h, _ptr(x0, C.c_uint64), first, count, model,
                                              C.c_void_p(dev_ptr)))
 
-    def clt_stream(self, init, first, count, model=MODEL_GATEWARE, noise_var=None):
+    def clt_stream(self, init, first, count, model=MODEL_GATEWARE, noise_var=None, out=None):
         x0 = state_words(init, self.n)
         if noise_var is None:
-            out = np.zeros(count, dtype=np.int8)
+            out = np.zeros(count, dtype=np.int8) if out is None else _check_out(out, np.int8, count)
             self._check(self._L.bbb_clt_stream(self._h, _ptr(x0, C.c_uint64), first, count, model, 1,
                                                _ptr(out, C.c_int8), None))
         else:
-            out = np.zeros(count, dtype=np.int16)
+            out = np.zeros(count, dtype=np.int16) if out is None else _check_out(out, np.int16, count)
             self._check(self._L.bbb_clt_stream(self._h, _ptr(x0, C.c_uint64), first, count, model,
                                                noise_var, None, _ptr(out, C.c_int16)))
         return out
@@ -300,8 +307,8 @@ class Context:
                                                    C.c_void_p(dev_ptr)))
 
     # ---- PRBS ------------------------------------------------------------------------------
-    def prbs_stream(self, k, nbits, state0=1, first_bit=0):
-        out = np.zeros(nbits // 64, dtype=np.uint64)
+    def prbs_stream(self, k, nbits, state0=1, first_bit=0, out=None):
+        out = np.zeros(nbits // 64, dtype=np.uint64) if out is None else _check_out(out, np.uint64, nbits // 64)
         self._check(self._L.bbb_prbs_stream(self._h, k, state0, first_bit, nbits,
                                             _ptr(out, C.c_uint64)))
         return out
@@ -334,7 +341,7 @@ class Context:
                                                    C.byref(det) if det is not None else None, C.byref(ctr)))
         return ctr.as_dict()
 
-    def tx_stream(self, k, nbits, coeff, first_bit=0, bit_en=1, init=None, noise_var=0, dev_ptr=None):
+    def tx_stream(self, k, nbits, coeff, first_bit=0, bit_en=1, init=None, noise_var=0, dev_ptr=None, out=None):
         """The 12-bit TX words (tx.py:52-81: shaped PRBS + CLT-GRNG * noise_var), 8 per bit, as int16.
         init None = noise off.  dev_ptr: write to device memory instead of returning an array."""
         cf = np.ascontiguousarray(coeff, dtype=np.int16)
@@ -345,7 +352,7 @@ class Context:
             self._check(self._L.bbb_tx_stream_dev(self._h, k, first_bit, nbits, _ptr(cf, C.c_int16), bit_en, px0,
                                                   noise_var, C.c_void_p(dev_ptr)))
             return None
-        out = np.zeros(nbits * 8, dtype=np.int16)
+        out = np.zeros(nbits * 8, dtype=np.int16) if out is None else _check_out(out, np.int16, nbits * 8)
         self._check(self._L.bbb_tx_stream(self._h, k, first_bit, nbits, _ptr(cf, C.c_int16), bit_en, px0, noise_var,
                                           _ptr(out, C.c_int16)))
         return out
