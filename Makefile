@@ -23,7 +23,7 @@ oracle:
 
 # drop-in for the reference's rnghunt binary (software/rnghunt/src/bin/rnghunt.rs), C++ over the C ABI
 cli/rnghunt: cli/rnghunt.cpp include/bbb_b200.h $(LIB)
-	g++ -O2 -std=c++17 -Wall -o $@ cli/rnghunt.cpp -Lbasebandboard_b200 -lbbb_b200 -Wl,-rpath,'$$ORIGIN/../basebandboard_b200'
+	g++ -O2 -std=c++17 -Wall -pthread -o $@ cli/rnghunt.cpp -Lbasebandboard_b200 -lbbb_b200 -Wl,-rpath,'$$ORIGIN/../basebandboard_b200'
 
 clean:
 	rm -rf build $(LIB) cli/rnghunt

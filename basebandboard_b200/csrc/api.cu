@@ -223,7 +223,14 @@ int bbb_stream_to_host(bbb_ctx *c, int dev_slot, void *out, size_t total, size_t
 
 extern "C" {
 
-int bbb_version(void) { return 100; }
+int bbb_version(void) { return 200; }
+
+int bbb_device_count(void)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) return 0;
+    return count;
+}
 
 int bbb_create(int device, bbb_ctx **out)
 {

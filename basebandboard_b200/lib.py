@@ -46,6 +46,7 @@ _ctx = C.c_void_p
 # name -> (restype, argtypes); every function include/bbb_b200.h declares
 SIGNATURES = {
     "bbb_version": (C.c_int, []),
+    "bbb_device_count": (C.c_int, []),
     "bbb_create": (C.c_int, [C.c_int, _P(_ctx)]),
     "bbb_destroy": (None, [_ctx]),
     "bbb_last_error": (C.c_char_p, [_ctx]),

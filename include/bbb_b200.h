@@ -62,6 +62,9 @@ typedef struct bbb_ctx bbb_ctx;
 
 /* ---- context ----------------------------------------------------------- */
 int  bbb_version(void);
+/* Number of CUDA devices visible to the process (0 if none / no driver): what a host sizes its pool of
+ * worker threads with, one ctx each -- the analogue of num_cpus::get() in rnghunt.rs:17. */
+int  bbb_device_count(void);
 /* Binds `device` (cudaSetDevice ordinal), creates the ctx's stream. */
 int  bbb_create(int device, bbb_ctx **out);
 void bbb_destroy(bbb_ctx *ctx);
