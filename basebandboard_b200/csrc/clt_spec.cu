@@ -583,6 +583,8 @@ clt256_words_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
 #define CLT256V2W_STAGE_WORDS (32 * 8 * CLT256V2_B)
 #define CLT256V2W_SMEM (CLT256V2_STATE_BYTES + CLT256V2W_STAGE_WORDS * 4)
 
+// stage word (stream j, word w) of thread `tid` lives in column tid ^ 16*(w >> 2): the two lanes that later
+// fetch the two halves of one thread's 32-byte piece then hit different banks
 #define CLT256V2_W_EMIT(w, r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18, r19, \
                         r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31)                                  \
     {                                                                                                                \
@@ -590,7 +592,7 @@ clt256_words_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
                            r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31};                          \
         transpose32_fast(tw);                                                                                        \
         _Pragma("unroll") for (int j = 0; j < 32; j++)                                                               \
-            asm volatile("st.shared.u32 [%0], %1;" ::"r"(stage_a + (uint32_t)((j * 8 + (w)) * CLT256V2_B * 4)), "r"(tw[j])); \
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(((w) < 4 ? stage_a : stage_b) + (uint32_t)((j * 8 + (w)) * CLT256V2_B * 4)), "r"(tw[j])); \
     }
 
 #ifndef CLT256V2W_STORE_KIND
@@ -619,8 +621,17 @@ clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
     const uint32_t t = blockIdx.x * CLT256V2_B + tid;
     uint32_t *const st = (uint32_t *)smem4 + tid;
     for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
-    const uint32_t stage_a = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES) + tid * 4u;
-    uint32_t *const outp = out + (size_t)t * 32u * L * 8u;   // stream j, clock it: outp + (j*L + it)*8
+    const uint32_t stage_base = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
+    const uint32_t stage_a = stage_base + tid * 4u, stage_b = stage_base + (tid ^ 16u) * 4u;
+    // store side: lanes 2q, 2q+1 write the two 16-byte halves of ONE stream's 32-byte clock, so a warp store covers
+    // 16 complete sectors (it was 32 half sectors when every lane stored its own thread's streams): lane (q, h)
+    // serves threads wbase + q and wbase + q + 16 of its warp
+    const uint32_t lane = tid & 31u, q = lane >> 1, h = lane & 1u, wbase = tid & ~31u;
+    const uint32_t u0 = wbase + q, u1 = u0 + 16u;
+    const uint32_t rd0 = stage_base + ((4u * h) * CLT256V2_B + (u0 ^ (16u * h))) * 4u;
+    const uint32_t rd1 = stage_base + ((4u * h) * CLT256V2_B + (u1 ^ (16u * h))) * 4u;
+    uint32_t *const op0 = out + (size_t)(blockIdx.x * CLT256V2_B + u0) * 32u * L * 8u + 4u * h;   // stream j, clock it: + (j*L + it)*8
+    uint32_t *const op1 = out + (size_t)(blockIdx.x * CLT256V2_B + u1) * 32u * L * 8u + 4u * h;
 #define CLT256V2_SECTION_RESIDENT_DECL
 #include "clt256_v2_gen.inc"
 #undef CLT256V2_SECTION_RESIDENT_DECL
@@ -630,23 +641,20 @@ clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #define CLT256V2_SECTION_W_BODY
 #include "clt256_v2_gen.inc"
 #undef CLT256V2_SECTION_W_BODY
-        uint32_t *const o32 = outp + (size_t)it * 8u;
+        __syncwarp();
 #pragma unroll 4
         for (int j = 0; j < 32; j++) {
             uint32_t v[8];
 #pragma unroll
-            for (int w = 0; w < 8; w++)
-                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[w]) : "r"(stage_a + (uint32_t)((j * 8 + w) * CLT256V2_B * 4)));
-#ifdef CLT256V2W_COALESCED_EXPERIMENT   /* wrong layout, same bytes: what the store pattern costs */
-            uint4 *const d0 = (uint4 *)out + ((size_t)(it * 32u + j) * 2u) * T + t;
-            CLT256V2W_STORE(d0, make_uint4(v[0], v[1], v[2], v[3]));
-            CLT256V2W_STORE(d0 + T, make_uint4(v[4], v[5], v[6], v[7]));
-#else
-            uint4 *const d = (uint4 *)(o32 + (size_t)j * L * 8u);
-            CLT256V2W_STORE(d, make_uint4(v[0], v[1], v[2], v[3]));
-            CLT256V2W_STORE(d + 1, make_uint4(v[4], v[5], v[6], v[7]));
-#endif
+            for (int i = 0; i < 4; i++) {
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[i]) : "r"(rd0 + (uint32_t)((j * 8 + i) * CLT256V2_B * 4)));
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[4 + i]) : "r"(rd1 + (uint32_t)((j * 8 + i) * CLT256V2_B * 4)));
+            }
+            const size_t off = ((size_t)j * L + it) * 8u;
+            CLT256V2W_STORE((uint4 *)(op0 + off), make_uint4(v[0], v[1], v[2], v[3]));
+            CLT256V2W_STORE((uint4 *)(op1 + off), make_uint4(v[4], v[5], v[6], v[7]));
         }
+        __syncwarp();
     }
 }
 
