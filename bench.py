@@ -390,6 +390,29 @@ def run_secondary(args, ctx, rank, world, local_rank):
                     "2^%d bits/GPU (SURVEY 8f-3)" % (args.k, args.log2_bits - 7))
         dtype = "int16 sums of 9-bit coefficients"
         l2 = "output (%d MiB) exceeds L2; nothing is read back" % ((nbits * 16) >> 20)
+    elif w == "lutopt_stream":
+        # BASELINE.json configs[4](ii): the raw URNG word of every clock (rng.py:27,38-40), 32 B per step
+        count = 1 << args.log2_steps
+        first = rank * count
+        ctx.lutopt_load_shipped(N_STATE)
+        buf = torch.empty(count * 4, dtype=torch.int64, device="cuda")
+        def step():
+            ctx.lutopt_stream_dev(1, first, count, buf.data_ptr())
+            return ctx.last_launches
+        host = {}
+        def step_e2e():
+            n = min(count, 1 << 27)
+            if "b" not in host:
+                import numpy as np
+                host["b"] = np.ones(n * 4, dtype=np.uint64)
+                return None
+            ctx.lutopt_stream(1, first, n, out=host["b"])
+            return n * 32, ctx.last_h2d_bytes, ctx.last_d2h_bytes
+        units, metric, unit, scale = count * 32, "lutopt_stream_gbytes_per_s", "GB/s", 1e-9
+        workload = ("raw LUTOPT-256 URNG words (init 1) materialised to HBM, 2^%d steps x 32 B per GPU "
+                    "(BASELINE.json configs[4]; rng.py:27)" % args.log2_steps)
+        dtype = "u32 (GF(2) bit ops)"
+        l2 = "output (%d MiB) exceeds L2; nothing is read back" % ((count * 32) >> 20)
     elif w == "clt_stream":
         count = 1 << args.log2_samples
         first = rank * count
@@ -427,7 +450,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
         dtype = "u32 GF(2)"
         l2 = "no HBM-resident input"
 
-    lop3_peak = max(ctx.measure_lop3_peak() for _ in range(3)) / 1e12 if w in ("prbs_slicer", "prbs_shaped_slicer", "clt_stream") else None
+    lop3_peak = max(ctx.measure_lop3_peak() for _ in range(3)) / 1e12 if w in ("prbs_slicer", "prbs_shaped_slicer", "clt_stream", "prbs_detect") else None
     for _ in range(args.warmup):
         step()
         ctx.sync()
@@ -485,6 +508,13 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                                 "for 8.59 GB of packed bits (the last lines are still in L2 at kernel end), 0.1 MB read",
                                 "note": "algorithmic bytes = 1/8 B per PRBS bit; peak = measured copy bandwidth "
                                         "(MEASURED_PEAKS.json), per GPU"}
+        if w == "lutopt_stream" and hbm_peak:
+            ach = units / (dev_ms / args.steps * 1e-3) / 1e9
+            line["roofline"] = {"bound": "hbm", "kernel": ctx.last_kernel, "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                                "frac": ach / hbm_peak, "traffic": None,
+                                "traffic_note": "see profiles/ for the ncu --set full capture of this kernel (dram bytes per launch)",
+                                "note": "algorithmic bytes = 32 B written per LUTOPT step (the 256-bit state, rng.py:27); "
+                                        "peak = measured copy bandwidth (MEASURED_PEAKS.json), per GPU"}
         if w == "clt_stream":
             # still integer-pipe bound when stored (30.8 thread-instr per byte), SURVEY 8d
             ach = value / world * 1e9 * 30.8125 / 1e12
@@ -505,6 +535,18 @@ def run_secondary(args, ctx, rank, world, local_rank):
                                         "peak = LOP3 issue rate measured live (bbb_measure_lop3_peak); ncu: the kernel's "
                                         "shared-memory pipe is the busier one (82 % of its wavefront peak, ALU 75 %), "
                                         "profiles/r1_dec_kernels_ncu_full.txt"}
+        if w == "prbs_detect":
+            # ALU-pipe work per 64-bit word: m channel draws x (3 xorshifts of a 64-bit value = 6 SHF + 6 LOP3, key add
+            # 2 IADD3, AND-accumulate 2 LOP3 = 16) + 8 for the PRBS word recurrence, the compare and the counters; the six
+            # 32-bit multiply-adds of a draw's two 64-bit multiplies run on the FMA pipe and are not counted
+            per_word = 16 * args.err_m + 8
+            ach = value / world * 1e12 / 64.0 * per_word / 1e12
+            line["roofline"] = {"bound": "alu", "kernel": "prbs_detect", "achieved": ach, "peak": lop3_peak,
+                                "unit": "T thread-instr/s (ALU pipe)", "frac": ach / lop3_peak if lop3_peak else None,
+                                "traffic": None, "alu_instr_per_64bit_word": per_word,
+                                "note": "algorithmic ALU-pipe instructions per 64-bit word = 16 x err_m (splitmix64 channel draws) "
+                                        "+ 8 (word recurrence, compare, counters); peak = LOP3 issue rate measured live "
+                                        "(bbb_measure_lop3_peak); no HBM traffic"}
         if "ctr" in extra:
             line["result_check"] = dict(extra["ctr"], rounds=extra["rounds"], runs=extra["runs"],
                                         final_state=list(extra["final"]), counters="all-reduced over the ranks")
@@ -565,11 +607,12 @@ def main():
                     help="samples per GPU: default 2^40 for clt_fused, 2^33 (int8) / 2^32 (int16) = 8 GiB for clt_stream")
     ap.add_argument("--workload", default="clt_fused",
                     choices=["clt_fused", "prbs_stream", "prbs_detect", "rnghunt", "prbs_slicer", "prbs_shaped_slicer", "clt_stream",
-                             "tx_stream"],
+                             "tx_stream", "lutopt_stream"],
                     help="clt_fused = the headline (BASELINE.json configs[2]); the others are the remaining "
                          "BASELINE configs, same JSON contract, their own metric")
     ap.add_argument("--k", type=int, default=31, help="PRBS order for the prbs_* workloads")
     ap.add_argument("--log2-bits", type=int, default=36, help="PRBS bits per GPU per step")
+    ap.add_argument("--log2-steps", type=int, default=28, help="lutopt_stream: LUTOPT steps (32 B each) per GPU per step")
     ap.add_argument("--err-m", type=int, default=10, help="prbs_detect channel error probability 2^-m")
     ap.add_argument("--amplitude", type=int, default=256, help="prbs_slicer: TX bit amplitude (12-bit word)")
     ap.add_argument("--noise-var", type=int, default=8, help="prbs_slicer: noise_var 0..15 (tx.py:75-76; reset value 8)")
