@@ -445,6 +445,20 @@ int bbb_lutopt_jump(bbb_ctx *c, const uint64_t *x_in, uint64_t e, uint64_t *x_ou
     return BBB_OK;
 }
 
+// CLTGRNG of one URNG word (rng.py:96-108): the alternating-difference tree = sum_i (-1)^popcount(i) x[i].
+// Host arithmetic on one state: what the hardware shows logn clocks after reset (clt(x0), rng.py:189-190), which
+// no sample index of the device stream reaches (g[i] = clt(A^(i+1) x0)).
+int bbb_clt_value(uint32_t n, const uint64_t *x, uint32_t model, int32_t *g)
+{
+    if (!x || !g || n < 2 || n > BBB_MAX_N || (n & (n - 1)) || model > 1) return BBB_EINVAL;
+    int32_t acc = 0;
+    for (uint32_t i = 0; i < n; i++)
+        if ((x[i >> 6] >> (i & 63)) & 1ull) acc += (__builtin_popcount(i) & 1) ? -1 : 1;
+    if (model == BBB_MODEL_GATEWARE && acc == (int32_t)(n / 2)) acc = -(int32_t)(n / 2);   // Signal((logn, True)), rng.py:78
+    *g = acc;
+    return BBB_OK;
+}
+
 // ---------------------------------------------------------------------------
 // clt-grng-evaluate.py:18-21 style statistics from the integer histogram
 // ---------------------------------------------------------------------------

@@ -1018,6 +1018,15 @@ shaped_slicer_err_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64
 
 // PRBS words covering absolute bits [origin, last) on the device (scratch slot 10); origin = 64 bits
 // before `first` when there are that many
+// Pulser (tx.py:20-31, clocked in the shaper's prbsclk domain, bitshaper.py:35): source bit m is 1 when m % 256 == 0
+__global__ void pulse_words_kernel(uint64_t *__restrict__ out, uint64_t org, uint64_t nwords)
+{
+    for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < nwords; j += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t b0 = (uint32_t)((256u - (uint32_t)((org + 64 * j) & 255u)) & 255u);
+        out[j] = b0 < 64u ? 1ull << b0 : 0ull;
+    }
+}
+
 static int shaper_tx_words(bbb_ctx *c, uint32_t k, uint64_t first, uint64_t nbits_with_lookahead, size_t extra_words,
                            uint64_t **d_tx, int64_t *origin)
 {
@@ -1025,7 +1034,16 @@ static int shaper_tx_words(bbb_ctx *c, uint32_t k, uint64_t first, uint64_t nbit
     const uint64_t span = ((first - org) + nbits_with_lookahead + 63) & ~63ull;
     uint64_t *d = (uint64_t *)c->scratch(10, (size_t)(span / 64 + extra_words + 1) * 8);   // + the word a window load may touch
     if (!d) return BBB_ECUDA;
-    int rc = bbb_prbs_stream_dev(c, k, 1u, org, span, d);
+    int rc = BBB_OK;
+    if (k == BBB_TX_SRC_PULSE) {
+        const uint64_t nwords = span / 64;
+        const uint64_t blocks = (nwords + 255) / 256, most = (uint64_t)c->sm_count * 8;
+        pulse_words_kernel<<<(uint32_t)(blocks < most ? (blocks ? blocks : 1) : most), 256, 0, c->stream>>>(d, org, nwords);
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+    } else {
+        rc = bbb_prbs_stream_dev(c, k, 1u, org, span, d);
+    }
     if (rc) return rc;
     *d_tx = d;
     *origin = (int64_t)org;
@@ -1047,8 +1065,10 @@ extern "C" {
 int bbb_tx_stream_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff, uint32_t bit_en,
                       const uint64_t *x0, uint32_t noise_var, int16_t *out_dev)
 {
-    int rc = check_prbs_args(c, k, 0);
+    if (!c) return BBB_EINVAL;
+    int rc = k == BBB_TX_SRC_PULSE ? BBB_OK : check_prbs_args(c, k, 0);
     if (rc) return rc;
+    BBB_CUDA(c, cudaSetDevice(c->device));
     ShaperCoef cf;
     rc = shaper_check(c, coeff, cf);
     if (rc) return rc;

@@ -18,6 +18,7 @@ SO_PATH = os.environ.get("BBB_B200_LIB") or os.path.join(_HERE, "libbbb_b200.so"
 MODEL_GATEWARE, MODEL_NUMPY = 0, 1
 STAGE_NAMES = ("degree", "filter", "order", "factor", "primitive")
 STAGE_PRIMITIVE = 4
+TX_SRC_PULSE = 0          # bbb_tx_stream(k = BBB_TX_SRC_PULSE): the Pulser source of tx.py:20-31,59-65
 
 
 class BBBError(RuntimeError):
@@ -74,6 +75,7 @@ SIGNATURES = {
                                      C.c_void_p, C.c_void_p]),
     "bbb_clt_stream_dec": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, _P(C.c_int8)]),
     "bbb_clt_stream_dec_dev": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]),
+    "bbb_clt_value": (C.c_int, [C.c_uint32, _u64p, C.c_uint32, _P(C.c_int32)]),
     "bbb_clt_stats": (C.c_int, [C.c_uint32, C.c_uint32, _u64p, _P(C.c_double)]),
     "bbb_prbs_tap": (C.c_uint32, [C.c_uint32]),
     "bbb_prbs_stream": (C.c_int, [_ctx, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, _u64p]),
@@ -429,6 +431,29 @@ def prbs_spec_state(k, first_bit, m=0, seed=1):
     if rc != 0:
         raise BBBError(rc, "bbb_prbs_spec_state(k=%d, first_bit=%d, m=%d)" % (k, first_bit, m))
     return det
+
+
+def clt_value(n, x, model=MODEL_GATEWARE):
+    """CLTGRNG of one URNG word (bbb_clt_value; host arithmetic, needs no GPU)."""
+    w = state_words(x, n)
+    g = C.c_int32(0)
+    rc = load().bbb_clt_value(n, _ptr(w, C.c_uint64), model, C.byref(g))
+    if rc != 0:
+        raise BBBError(rc, "bbb_clt_value(n=%d)" % n)
+    return int(g.value)
+
+
+def hw_latency_split(n, first, count):
+    """The hardware's output sequence (rng.py:70-72,189-190): hw[h] = 0 for h < log2(n) (reset registers),
+    hw[log2 n] = clt(x0), hw[log2 n + 1 + i] = g[i].  For samples hw[first, first+count) returns
+    (number of leading zeros, whether clt(x0) is included, first g index, number of g samples)."""
+    logn = n.bit_length() - 1
+    end = first + count
+    zeros = max(0, min(end, logn) - first)
+    has_x0 = first <= logn < end
+    g_lo = max(first, logn + 1)
+    g_cnt = max(0, end - g_lo)
+    return zeros, has_x0, g_lo - (logn + 1), g_cnt
 
 
 def clt_stats(n, hist, model=MODEL_GATEWARE):

@@ -7,7 +7,9 @@ plots; here the bits come from the gateware's own uniform generator, LUTOPT(n256
 (gateware/bbb/tx.py:70-71), the samples are produced and histogrammed on the GPU, and the plot is
 replaced by numbers (--hist prints the unit-width histogram the reference would draw, :34).
 
-  --n N --nsamp COUNT --init X --first I --model gateware|numpy --hist --stats --gpu D
+  --n N --nsamp COUNT --init X --first I --model gateware|numpy --hist --stats --gpu D --hw-latency
+  --hw-latency  the sequence the hardware emits after reset instead of g[first..]: log2(n) zeros (the reset
+                value of the pipeline registers), clt(x0), then g[0], g[1], ... (gateware/bbb/rng.py:70-72,189-190)
 """
 import argparse
 import math
@@ -27,13 +29,22 @@ def main():
     ap.add_argument("--hist", action="store_true")
     ap.add_argument("--stats", action="store_true")
     ap.add_argument("--gpu", type=int, default=0)
+    ap.add_argument("--hw-latency", action="store_true")
     a = ap.parse_args()
     from basebandboard_b200 import lib
     logn = int(math.log2(a.n))
     model = lib.MODEL_NUMPY if a.model == "numpy" else lib.MODEL_GATEWARE
+    zeros, has_x0, g_first, g_count = (0, False, a.first, a.nsamp)
+    if a.hw_latency:
+        zeros, has_x0, g_first, g_count = lib.hw_latency_split(a.n, a.first, a.nsamp)
     with lib.Context(a.gpu) as c:
         c.lutopt_load_shipped(a.n)
-        hist, s1, s2 = c.clt_hist(a.init, a.first, a.nsamp, model)
+        hist, s1, s2 = c.clt_hist(a.init, g_first, g_count, model)
+    extra = [0] * zeros + ([lib.clt_value(a.n, a.init, model)] if has_x0 else [])
+    for g in extra:                                        # the start-up samples the device stream does not hold
+        hist[g + a.n // 2] += 1
+        s1 += g
+        s2 += g * g
     mu_s = s1 / a.nsamp                                    # np.mean  (:19)
     var_s = s2 / a.nsamp - mu_s * mu_s                     # np.var, ddof = 0  (:21)
     mu_t, var_t = 0, float(2 ** (logn - 2))                # :18, :20

@@ -141,6 +141,9 @@ int bbb_clt_stream_dec(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_
                        uint32_t delay, int8_t *out8);
 int bbb_clt_stream_dec_dev(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t spb,
                            uint32_t delay, int8_t *out8_dev);
+/* CLTGRNG of ONE URNG word x (rng.py:96-108), pure host arithmetic.  For the hardware's start-up: after reset
+ * CLTGRNG.x shows log2(n) zeros (reset registers), then clt(x0), then g[0], g[1], ... (rng.py:70-72,189-190). */
+int bbb_clt_value(uint32_t n, const uint64_t *x, uint32_t model, int32_t *g);
 /* clt-grng-evaluate.py:18-21 from an integer histogram, in f64 with a fixed
  * summation order: stats[0]=mean, [1]=variance (ddof=0), [2]=excess kurtosis,
  * [3]=chi-square against N(0, n/4) bin probabilities, [4]=chi-square against the
@@ -201,7 +204,10 @@ int bbb_prbs_slicer_detect(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_
  * shift register's reset value); the HDL's 13-clock pipeline latency is dropped.
  * out[t - 8*first_bit] = the 12-bit signed TX word (tx.py:80-81) x[t] = bit_en*S[t] + g[t]*noise_var,
  * wrapped to 12 bits, stored as int16, for t in [8*first_bit, 8*(first_bit+nbits)); g = CLT-GRNG of
- * the loaded recurrence from init x0 (x0 NULL = noise off). */
+ * the loaded recurrence from init x0 (x0 NULL = noise off).
+ * k = BBB_TX_SRC_PULSE selects the other source of tx.py:59-65 (src_sel = 1): the Pulser (tx.py:20-31), whose
+ * bit m is 1 when m % 256 == 0, through the same shaper. */
+#define BBB_TX_SRC_PULSE 0
 int bbb_tx_stream(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff,
                   uint32_t bit_en, const uint64_t *x0, uint32_t noise_var, int16_t *out);
 int bbb_tx_stream_dev(bbb_ctx *ctx, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff,

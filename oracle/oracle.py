@@ -494,6 +494,13 @@ def shaper_stream(tx_bits, coeff):
     return f[64:]
 
 
+def pulser_bits(first, nbits):
+    """Pulser (tx.py:20-31) in the shaper's bit-clock domain (bitshaper.py:35): an 8-bit counter from 0,
+    x = (counter == 0) -> source bit m is 1 when m % 256 == 0.  Returns bits [first, first+nbits) as 0/1."""
+    m = np.arange(first, first + nbits, dtype=np.int64)
+    return (m % 256 == 0).astype(np.uint8)
+
+
 def tx_words(shaped, g, noise_var, bit_en=1):
     """tx.py:75-81: x = bitmux + noisemux registered as Signal((12, True)) -> wraps to 12 bits."""
     x = (np.asarray(shaped, dtype=np.int64) if bit_en else 0) + np.asarray(g, dtype=np.int64) * int(noise_var)

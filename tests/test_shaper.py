@@ -69,6 +69,29 @@ def test_tx_stream_matches_oracle(gold, orc, k, sel, first, nv):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("sel,first,nv", [(16, 0, 0), (0, 250, 8), (31, 64 * 1000 + 3, 15)])
+def test_tx_stream_pulser_source_matches_oracle(gold, orc, sel, first, nv):
+    """tx.py:59-65 with src_sel = 1: the Pulser (tx.py:20-31; one 1 bit every 256 bit periods) through the same
+    shaper -- bbb_tx_stream with k = BBB_TX_SRC_PULSE."""
+    from basebandboard_b200 import lib, recurrences
+    coeff = gold["tx_sets"][sel]
+    nbits = 64 * 40 + 17
+    with lib.Context(0) as c:
+        c.lutopt_load_shipped(256)
+        c.set_tuning("slicer_chunk_bits", 64 * 16)
+        got = c.tx_stream(lib.TX_SRC_PULSE, nbits, coeff, first_bit=first, init=1 if nv else None, noise_var=nv)
+    start = max(first - 8, 0)
+    hist = [0] * (8 - (first - start)) + orc.pulser_bits(start, first - start + nbits).tolist()
+    S = orc.shaper_stream(hist, coeff)
+    g = orc.clt_run(recurrences.packed(256), 1, first * 8, nbits * 8, model=0, want=("out8",))["out8"]
+    assert np.array_equal(got, orc.tx_words(S, g, nv))
+    if first == 0 and nv == 0:
+        # between pulses every register bit is 0: the steady word is minus the sum of the taps at phase t % 8
+        cc = np.array(coeff)
+        assert got[8 * 20] == -int(cc[4::8].sum())
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("k,sel,delay,nv,first", [(15, 10, 4, 15, 0), (7, 31, 2, 15, 64 * 50), (31, 0, 7, 8, 12345), (23, 32, 0, 15, 1)])
 def test_shaped_slicer_loop_matches_oracle(gold, orc, k, sel, delay, nv, first):
     """decisions on x[8(J+4)+delay] vs b[J], then PRBSErrorDetector: == oracle composition"""
