@@ -362,6 +362,18 @@ __global__ void hunt_front_kernel(FrontParams p)
 // few survivors) goes to global memory.
 // shared: taps[n][CPW+1] words, seq[ceil(2n/32)][CPW] words
 // ---------------------------------------------------------------------------
+// ballot of (x & 1) over the warp: the AND and the predicate in ONE LOP3 (its predicate output), then the vote --
+// written out because the compiler spends LOP3 + ISETP on `__ballot_sync(~0u, x & 1)`
+__device__ __forceinline__ uint32_t ballot_odd(uint32_t x)
+{
+    uint32_t r;
+    asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b32 d;\n\tsetp.ne.u32 q, 0, 0;\n\t"
+                 "lop3.or.b32 d|p, %1, 1, 0, 0xc0, q;\n\t"
+                 "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t}"
+                 : "=r"(r) : "r"(x));
+    return r;
+}
+
 template <int NW, int CPW>
 __global__ void __launch_bounds__(32, 8)
 hunt_front_warp_kernel(FrontParams p)
@@ -424,7 +436,7 @@ hunt_front_warp_kernel(FrontParams p)
                     uint32_t v = W[0] & M[j][0];
 #pragma unroll
                     for (int w = 1; w < NW; w++) v ^= W[w] & M[j][w];
-                    Wn[j] = __ballot_sync(0xffffffffu, __popc(v) & 1u);
+                    Wn[j] = ballot_odd(__popc(v));
                 }
 #pragma unroll
                 for (int w = 0; w < NW; w++) W[w] = Wn[w];
