@@ -80,6 +80,17 @@ def test_rnghunt_n192_interleaved_shards_merge_to_the_same_ranking(ctx):
 # ------------------------------------------------------------------------------------------------
 # configs[1]: PRBS generate + detect
 # ------------------------------------------------------------------------------------------------
+TAPS = {7: 6, 9: 5, 11: 9, 15: 14, 20: 3, 23: 18, 31: 28}          # prbs.py:14
+
+
+def test_oracle_jump_equals_stepping(orc):
+    """the jump used below == clocking the oracle's PRBS bit by bit (prbs.py:112-113)"""
+    for k in (7, 15, 23, 31):
+        rows = [[k - 1, TAPS[k] - 1]] + [[i - 1] for i in range(1, k)]
+        for first in (0, 1, 63, 1000, 123457):
+            assert orc.lutopt_jump(rows, 1, first) == orc.lib().orc_prbs_advance(k, 1, first)
+
+
 def _det_tuple(d):
     return (int(d.bit_in), int(d.prbs), int(d.err_sr), int(d.reload_ctr))
 
@@ -112,7 +123,11 @@ def test_prbs_detect_random_2p24_windows_from_the_locked_state(ctx, orc):
             det = lib.DetState(*_det_tuple(spec))
             got = ctx.prbs_detect(k, 1 << 24, m=10, seed=1, first_bit=first, det=det)
             odet = orc.DetState(*_det_tuple(spec))
-            want, _, wdet = orc.prbs_detect(k, 1 << 24, m=10, seed=1, first_bit=first, det=odet)
+            # generator state at `first` from the oracle's own GF(2) jump-ahead on the LFSR written as a recurrence
+            # matrix (prbs.py:28-35: new bit 0 = s[k-1] ^ s[tap-1], bit i = s[i-1]); stepping 2^36 bits would take minutes
+            rows = [[k - 1, TAPS[k] - 1]] + [[i - 1] for i in range(1, k)]
+            gen = orc.lutopt_jump(rows, 1, first)
+            want, _, wdet = orc.prbs_detect(k, 1 << 24, m=10, seed=1, first_bit=first, gen_state=gen, det=odet)
             assert got == want, (k, first)
             assert _det_tuple(det) == _det_tuple(wdet), (k, first)
 
