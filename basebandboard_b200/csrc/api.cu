@@ -323,6 +323,7 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
     else if (!strcmp(key, "hunt_batch")) c->tune_hunt_batch = value < 0 ? 0u : (uint32_t)value;
     else if (!strcmp(key, "stream_chunk_bytes")) c->tune_stream_chunk = value < 0 ? 0ull : (uint64_t)value;
     else if (!strcmp(key, "host_copy_threads")) c->tune_host_copy_threads = value < 0 ? 0u : (uint32_t)value;
+    else if (!strcmp(key, "hunt_pow_k")) c->tune_hunt_pow_k = value == 4 ? 4u : 0u;
     else if (!strcmp(key, "hunt_cpw")) c->tune_hunt_cpw = value == 16 ? 16u : 0u;
     else if (!strcmp(key, "prbs_stream_reps")) c->tune_prbs_stream_reps = value < 0 ? 0u : (uint32_t)value;
     else return c->fail(BBB_EINVAL, "unknown tuning key %s", key);

@@ -66,6 +66,7 @@ struct bbb_ctx {
     uint32_t tune_hunt_batch = 0;       // 0: 2^20 candidates per rnghunt batch
     uint64_t tune_stream_chunk = 0;     // bytes per chunk of the host-buffer stream calls (0: 64 MiB / 256 MiB)
     uint32_t tune_host_copy_threads = 0; // threads copying a chunk out of the pinned staging buffer (0: up to 8)
+    uint32_t tune_hunt_pow_k = 0;       // clocks per pass of hunt_front_pow_kernel: 0/8, or 4
     uint32_t tune_hunt_cpw = 0;         // candidates per warp pass of hunt_front_warp_kernel: 0/32, or 16
     uint32_t last_rounds = 0;           // kernel rounds of the last bbb_prbs_detect
     // PRBS jump tables per k (prbs.cu), built on first use

@@ -269,6 +269,8 @@ struct FrontParams {
     uint32_t count;
     HuntOut out;
     uint16_t *dump_taps;   // [n][4] taps of candidate `first` (bbb_rnghunt_candidate), else null
+    uint32_t *tap_scratch; // hunt_front_pow_kernel: [grid][n][32] words, private to the launch
+    uint32_t *group_counter;   // hunt_front_pow_kernel: zeroed before the launch
 };
 
 // shared memory: state bytes xs[(n+1)][B] words, then taps[n][B] (4 x TapT per thread and row)
@@ -458,6 +460,183 @@ hunt_front_warp_kernel(FrontParams p)
             for (uint32_t st = 0; st < nb; st++) bm.push((word >> (31u - st)) & 1u);
         }
         hunt_finish<NWP>(p.out, n, slot0 + lane, bm.c, bm.l);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// front kernel, one warp per candidate, K clocks per pass (n <= 256): the product path.
+//
+// With rows kept as dense masks the cost of x -> M.x does not depend on how sparse M is, so the warp applies
+// P = A^K instead of A: one pass of NW*NW LOP3 + NW votes advances the state K clocks.  The output bits of the
+// K-1 clocks in between, u[t+i] = (row 0 of A^i) . x[t] (binary_matrix.rs:72-73 emits x[0] after every step), come
+// from one more row group: lane i-1 holds row 0 of A^i as its "extra" row, and one more vote returns all of them.
+// A block of K clocks is therefore (NW+1) * (NW + 3) warp instructions, where hunt_front_warp_kernel spends
+// K * NW * (NW + 3).  The powers are built by K-1 sparse left multiplications P <- A.P: the rows of P lie in
+// shared memory (48-byte row stride: conflict-light 128-bit gathers), lane l XORs the four rows its row of A taps
+// (an empty tap slot repeats the previous pick and is skipped), for each of its NW rows.
+//
+// Persistent warps (one per CTA) pull groups of 32 candidates from an atomic counter.  Generation and
+// Berlekamp-Massey run thread-per-candidate around the warp phase as in hunt_front_warp_kernel; the generated
+// tap lists wait in a per-warp global scratch ([row][32] words, 24 KB at n = 192, re-used by every group the
+// warp takes, so it lives in L2 and shared memory stays small enough for 16 warps per SM).
+// shared: pow[n][RS] words, seq[ceil(2n/32)][32] words (bit t of a candidate's sequence = word t/32, bit t%32)
+// ---------------------------------------------------------------------------
+template <int NW, int K>
+__global__ void __launch_bounds__(32, (NW <= 6 ? 16 : 8))
+hunt_front_pow_kernel(FrontParams p)
+{
+    uint32_t *const tap_scratch = p.tap_scratch;
+    uint32_t *const group_counter = p.group_counter;
+    constexpr int NWP = NW + 1;
+    constexpr int RW = NW <= 4 ? 4 : 8;                    // words per row of P in shared memory
+    constexpr int RS = NW <= 4 ? 4 : 12;                   // row stride: an odd number of 16-byte units per 4 words read
+    static_assert(32 % K == 0 && K >= 2, "K must divide 32");
+    extern __shared__ __align__(16) uint32_t hsm[];
+    const uint32_t lane = threadIdx.x, n = p.n;
+    const uint32_t SW = (2 * n + 31) / 32;                 // sequence words per candidate
+    uint32_t *pw = hsm;
+    uint32_t *seq = hsm + (size_t)n * RS;
+    uint32_t *taps = tap_scratch + (size_t)blockIdx.x * n * 32u;
+    const uint32_t ngroups = (p.count + 31u) / 32u;
+
+    for (;;) {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(group_counter, 1u);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= ngroups) break;
+        const uint32_t slot0 = g * 32u;
+        const uint32_t ncand = p.count - slot0 < 32u ? p.count - slot0 : 32u;
+
+        // phase 1: lane c generates candidate slot0 + c (binary_matrix.rs:81-101)
+        if (lane < ncand) {
+            const uint64_t cand = p.first + (uint64_t)(slot0 + lane) * p.stride;
+            uint32_t acc = 0, prev = 0;
+            hunt_generate<NW>(n, p.seed, cand, [&](uint32_t row, uint32_t k, uint32_t col) {
+                const uint32_t cc = col == n ? prev : col;     // empty slot: repeat the previous pick
+                prev = cc;
+                acc |= cc << (8 * k);
+                if (k == 3) { __stcg(taps + row * 32u + lane, acc); acc = 0; }
+            });
+        }
+        __syncwarp();
+
+        // phase 2: one candidate at a time
+        for (uint32_t c = 0; c < ncand; c++) {
+            uint32_t T[NW], M[NW][NW], E[NW];
+#pragma unroll
+            for (int w = 0; w < NW; w++) E[w] = 0;
+#pragma unroll
+            for (int j = 0; j < NW; j++) {
+                const uint32_t row = lane + 32u * j;
+                T[j] = row < n ? __ldcg(taps + row * 32u + c) : 0xffffffffu;   // rows >= n: four repeated picks of column 255 ...
+#pragma unroll
+                for (int w = 0; w < NW; w++) M[j][w] = 0;
+                if (row < n) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const uint32_t t = (T[j] >> (8 * k)) & 0xffu, bit = 1u << (t & 31u);
+#pragma unroll
+                        for (int w = 0; w < NW; w++) M[j][w] |= (t >> 5) == (uint32_t)w ? bit : 0u;
+                    }
+                }
+            }
+            // M = rows of A.  K-1 times: publish P, note row 0 of P = A^i for lane i-1, P <- A.P
+#pragma unroll 1
+            for (uint32_t i = 1; i < (uint32_t)K; i++) {
+#pragma unroll
+                for (int j = 0; j < NW; j++) {
+                    const uint32_t row = lane + 32u * j;
+                    if (row < n) {
+                        uint32_t *dst = pw + (size_t)row * RS;
+                        if (RW == 4) {
+                            *(uint4 *)dst = make_uint4(M[j][0], NW > 1 ? M[j][NW > 1 ? 1 : 0] : 0u, NW > 2 ? M[j][NW > 2 ? 2 : 0] : 0u,
+                                                       NW > 3 ? M[j][NW > 3 ? 3 : 0] : 0u);
+                        } else {
+                            *(uint4 *)dst = make_uint4(M[j][0], M[j][NW > 1 ? 1 : 0], M[j][NW > 2 ? 2 : 0], M[j][NW > 3 ? 3 : 0]);
+                            *(uint4 *)(dst + 4) = make_uint4(M[j][NW > 4 ? 4 : 0], NW > 5 ? M[j][NW > 5 ? 5 : 0] : 0u,
+                                                             NW > 6 ? M[j][NW > 6 ? 6 : 0] : 0u, NW > 7 ? M[j][NW > 7 ? 7 : 0] : 0u);
+                        }
+                    }
+                }
+                __syncwarp();
+                {
+                    const uint4 e0 = *(const uint4 *)pw;
+                    uint4 e1 = make_uint4(0, 0, 0, 0);
+                    if (RW == 8) e1 = *(const uint4 *)(pw + 4);
+                    const uint32_t ev[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+                    if (lane == i - 1u) {
+#pragma unroll
+                        for (int w = 0; w < NW; w++) E[w] = ev[w];
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < NW; j++) {
+                    uint32_t a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                    if (lane + 32u * j < n) {
+#pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            const uint32_t t = (T[j] >> (8 * k)) & 0xffu;
+                            const uint32_t keep = (k == 0 || t != ((T[j] >> (8 * (k > 0 ? k - 1 : 0))) & 0xffu)) ? 0xffffffffu : 0u;
+                            const uint32_t *src = pw + (size_t)t * RS;
+                            const uint4 v0 = *(const uint4 *)src;
+                            a[0] ^= v0.x & keep; a[1] ^= v0.y & keep; a[2] ^= v0.z & keep; a[3] ^= v0.w & keep;
+                            if (RW == 8) {
+                                const uint4 v1 = *(const uint4 *)(src + 4);
+                                a[4] ^= v1.x & keep; a[5] ^= v1.y & keep; a[6] ^= v1.z & keep; a[7] ^= v1.w & keep;
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int w = 0; w < NW; w++) M[j][w] = a[w];
+                }
+                __syncwarp();
+            }
+            // M = rows of A^K, E (lanes 0..K-2) = row 0 of A^(lane+1)
+            uint32_t W[NW];
+#pragma unroll
+            for (int w = 0; w < NW; w++) {
+                const uint32_t lo = (uint32_t)w * 32u;
+                W[w] = n >= lo + 32 ? 0xffffffffu : (n > lo ? (1u << (n - lo)) - 1u : 0u);   // b = all ones (rnghunt.rs:28)
+            }
+            uint32_t mine = 0;
+            for (uint32_t ch = 0; ch < SW; ch++) {
+                uint32_t acc = 0;
+#pragma unroll
+                for (int q = 0; q < 32 / K; q++) {
+                    uint32_t Wn[NW];
+#pragma unroll
+                    for (int j = 0; j < NW; j++) {
+                        uint32_t v = W[0] & M[j][0];
+#pragma unroll
+                        for (int w = 1; w < NW; w++) v ^= W[w] & M[j][w];
+                        Wn[j] = ballot_odd(__popc(v));
+                    }
+                    uint32_t x = W[0] & E[0];
+#pragma unroll
+                    for (int w = 1; w < NW; w++) x ^= W[w] & E[w];
+                    const uint32_t X = ballot_odd(__popc(x));                 // bit i-1 = u[t+i], i < K
+#pragma unroll
+                    for (int w = 0; w < NW; w++) W[w] = Wn[w];
+                    acc |= (X | ((W[0] & 1u) << (K - 1))) << (q * K);         // u[t+K] = x[0] of the new state
+                }
+                if (lane == ch) mine = acc;
+            }
+            if (lane < SW) seq[lane * 32u + c] = mine;
+        }
+        __syncwarp();
+
+        // phase 3: lane c runs Berlekamp-Massey over candidate c's 2n bits (berlekamp_massey.rs:5-31)
+        if (lane < ncand) {
+            HuntBM<NWP> bm;
+            bm.init();
+            for (uint32_t ch = 0; ch < SW; ch++) {
+                const uint32_t word = seq[ch * 32u + lane];
+                const uint32_t nb = 2 * n - 32 * ch < 32u ? 2 * n - 32 * ch : 32u;
+                for (uint32_t st = 0; st < nb; st++) bm.push((word >> st) & 1u);
+            }
+            hunt_finish<NWP>(p.out, n, slot0 + lane, bm.c, bm.l);
+        }
+        __syncwarp();
     }
 }
 
@@ -911,11 +1090,45 @@ static int hunt_collect(bbb_ctx *c, HuntSlot &b, uint64_t stride, uint32_t nwp, 
     return BBB_OK;
 }
 
+// persistent warps of hunt_front_pow_kernel: one per CTA, up to 16 per SM
+static uint32_t hunt_pow_grid(const bbb_ctx *c, uint32_t count)
+{
+    const uint32_t groups = (count + 31u) / 32u, most = (uint32_t)c->sm_count * 16u;   // n > 192: 8 are resident, the rest queue
+    return groups < most ? (groups ? groups : 1u) : most;
+}
+
 static int launch_front(bbb_ctx *c, cudaStream_t st, const FrontParams &p)
 {
     const uint32_t n = p.n, nw = (n + 31) / 32;
-    // n <= 256: warp per candidate (state in registers, no gathers); "hunt_smem_taps" = 1 forces the
-    // thread-per-candidate kernel (tests: the two are independent implementations)
+    // n <= 256: warp per candidate, K clocks per pass ("hunt_pow_k" = 4 or 8); "hunt_smem_taps" = 2 selects the
+    // one-clock-per-pass warp kernel, 1 the thread-per-candidate kernel (tests: independent implementations)
+    if (!p.dump_taps && nw <= 8 && c->tune_hunt_smem_taps == 0 && p.tap_scratch) {
+        const uint32_t K = c->tune_hunt_pow_k == 4 ? 4 : 8;
+        const uint32_t rs = nw <= 4 ? 4 : 12;
+        const size_t smem = ((size_t)n * rs + (size_t)((2 * n + 31) / 32) * 32) * 4;
+        const uint32_t blocks = hunt_pow_grid(c, p.count);
+#define FRONT_POW_CASE(NW)                                                                                          \
+    case NW:                                                                                                        \
+        if (K == 8) {                                                                                               \
+            BBB_CUDA(c, cudaFuncSetAttribute(hunt_front_pow_kernel<NW, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                             (int)smem));                                                           \
+            hunt_front_pow_kernel<NW, 8><<<blocks, 32, smem, st>>>(p);                                              \
+        } else {                                                                                                    \
+            BBB_CUDA(c, cudaFuncSetAttribute(hunt_front_pow_kernel<NW, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                             (int)smem));                                                           \
+            hunt_front_pow_kernel<NW, 4><<<blocks, 32, smem, st>>>(p);                                              \
+        }                                                                                                           \
+        break
+        switch (nw) {
+            FRONT_POW_CASE(1); FRONT_POW_CASE(2); FRONT_POW_CASE(3); FRONT_POW_CASE(4); FRONT_POW_CASE(5);
+            FRONT_POW_CASE(6); FRONT_POW_CASE(7); FRONT_POW_CASE(8);
+        default: break;
+        }
+#undef FRONT_POW_CASE
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        return BBB_OK;
+    }
     if (!p.dump_taps && nw <= 8 && c->tune_hunt_smem_taps != 1) {
         const uint32_t cpw = c->tune_hunt_cpw == 16 ? 16 : 32;
         const size_t smem = ((size_t)n * (cpw + 1) + (size_t)((2 * n + 31) / 32) * cpw) * 4;
@@ -1026,6 +1239,14 @@ static int hunt_sweep(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uin
         p.n = n; p.seed = seed; p.first = first + done * stride; p.stride = stride; p.count = nb;
         p.out.stage = b.stage; p.out.surv_count = b.counters; p.out.surv_cand = b.surv_cand;
         p.out.surv_poly = b.surv_poly; p.out.poly_out = nullptr; p.dump_taps = nullptr;
+        p.group_counter = b.counters + 3;
+        p.tap_scratch = nullptr;
+        if (n <= 256) {      // per-slot scratch: the two slots' front kernels may overlap
+            const size_t per_slot = (size_t)hunt_pow_grid(c, cap) * n * 32 * 4;
+            char *ts = (char *)c->scratch(8, 2 * per_slot);
+            if (!ts) return BBB_ECUDA;
+            p.tap_scratch = (uint32_t *)(ts + turn * per_slot);
+        }
         b.first = p.first;
         rc = launch_front(c, b.stream, p);
         if (rc) return rc;

@@ -88,8 +88,10 @@ uint32_t bbb_last_rounds(const bbb_ctx *ctx);
 /* Tuning knobs, for tests and experiments (results never depend on them):
  *   "clt_no_spec" (0/1), "clt_spec_min_steps", "clt_spec_max_blocks",
  *   "prbs_chunk_words", "prbs_stream_reps", "hunt_batch", "hunt_slow_check" (0/1),
- *   "hunt_smem_taps" (0 auto, 1 thread-per-candidate kernel with shared-memory taps for every n),
- *   "hunt_cpw" (candidates per warp pass of the warp-per-candidate kernel: 32 or 16). */
+ *   "hunt_smem_taps" (0 auto = warp per candidate, K clocks per pass; 1 thread-per-candidate kernel with
+ *   shared-memory taps for every n; 2 warp per candidate, one clock per pass), "hunt_pow_k" (K: 8 or 4),
+ *   "hunt_cpw" (candidates per warp pass of the one-clock warp kernel: 32 or 16),
+ *   "stream_chunk_bytes", "host_copy_threads" (host-buffer stream calls). */
 int  bbb_set_tuning(bbb_ctx *ctx, const char *key, int64_t value);
 /* Region timer: CUDA events on the ctx's stream around any number of calls.
  * bbb_timer_stop waits for the stream and returns the device time in ms. */

@@ -166,23 +166,41 @@ def test_table_and_shift_add_primitivity_kernels_agree(ctx, n):
     assert fast["stage_counts"][STAGE_ORDER] > 0
 
 
-@pytest.mark.parametrize("n", [8, 16, 33, 100, 192, 250, 256])
-def test_warp_and_thread_front_kernels_agree(ctx, n):
-    """hunt_front_warp_kernel (one warp per candidate, row masks in registers, n <= 256; both widths of the
-    generation pass) vs hunt_front_kernel (one thread per candidate, byte state + tap lists in shared memory):
-    two independent implementations of binary_matrix.rs:53-76 + berlekamp_massey.rs:5-31."""
+@pytest.mark.parametrize("n", [8, 16, 33, 100, 128, 192, 250, 256])
+def test_power_warp_and_thread_front_kernels_agree(ctx, n):
+    """Three independent implementations of binary_matrix.rs:53-76 + berlekamp_massey.rs:5-31:
+    hunt_front_pow_kernel (one warp per candidate, A^K applied per pass with K = 8 and K = 4, K-1 extra rows for the
+    output bits in between), hunt_front_warp_kernel (one clock per pass; both widths of its generation pass) and
+    hunt_front_kernel (one thread per candidate, byte state + tap lists in shared memory)."""
     count = 5000 if n < 250 else 1500
-    a = ctx.rnghunt_sweep(n, 21, 7, count, k=8, want_stages=True)
-    ctx.set_tuning("hunt_cpw", 16)
-    a16 = ctx.rnghunt_sweep(n, 21, 7, count, k=8, want_stages=True)
-    ctx.set_tuning("hunt_cpw", 0)
-    ctx.set_tuning("hunt_smem_taps", 1)
+    runs = {}
+    for name, knobs in (("pow8", {}), ("pow4", {"hunt_pow_k": 4}), ("warp32", {"hunt_smem_taps": 2}),
+                        ("warp16", {"hunt_smem_taps": 2, "hunt_cpw": 16}), ("thread", {"hunt_smem_taps": 1})):
+        for k, v in knobs.items():
+            ctx.set_tuning(k, v)
+        try:
+            runs[name] = ctx.rnghunt_sweep(n, 21, 7, count, k=8, want_stages=True)
+        finally:
+            for k in knobs:
+                ctx.set_tuning(k, 0)
+    ref = runs["thread"]
+    for name, r in runs.items():
+        assert np.array_equal(r["stages"], ref["stages"]) and r["best"] == ref["best"], name
+        assert np.array_equal(r["stage_counts"], ref["stage_counts"]), name
+
+
+def test_power_kernel_ragged_batches_and_strides(ctx, orc):
+    """Group counts that are not multiples of 32, several batches, interleaved candidates: == oracle."""
+    n, seed = 64, 9
+    stages, _ = orc.rnghunt_sweep(n, seed, 0, 3000, threads=os.cpu_count() or 1)
+    ctx.set_tuning("hunt_batch", 1000 + 37)
     try:
-        b = ctx.rnghunt_sweep(n, 21, 7, count, k=8, want_stages=True)
+        for stride, first in ((1, 0), (3, 1), (7, 5)):
+            cnt = len(range(first, 3000, stride))
+            got = ctx.rnghunt_sweep(n, seed, first, cnt, k=4, stride=stride, want_stages=True)
+            assert np.array_equal(got["stages"], stages[first::stride])
     finally:
-        ctx.set_tuning("hunt_smem_taps", 0)
-    assert np.array_equal(a["stages"], b["stages"]) and a["best"] == b["best"]
-    assert np.array_equal(a16["stages"], b["stages"]) and a16["best"] == b["best"]
+        ctx.set_tuning("hunt_batch", 0)
 
 
 @pytest.mark.parametrize("n", [16, 64, 192])

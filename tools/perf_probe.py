@@ -59,17 +59,19 @@ def main():
                               "Gsamples_s": count / min(ms) / 1e6}), flush=True)
             del buf
     if "rnghunt" in what:
-        for cpw in (32, 16):
-            c.set_tuning("hunt_cpw", cpw)
+        for name, knobs in (("pow8", {}), ("pow4", {"hunt_pow_k": 4}), ("warp1", {"hunt_smem_taps": 2})):
+            for k, v in knobs.items():
+                c.set_tuning(k, v)
             for n in (64, 128, 192, 256):
-                cnt = 1 << 21 if n <= 192 else 1 << 19
-                c.rnghunt_sweep(n, 1, 0, 1 << 12, k=16)
+                cnt = 1 << 22 if n <= 192 else 1 << 20
+                c.rnghunt_sweep(n, 1, 0, 1 << 14, k=16)
                 r = c.rnghunt_sweep(n, 1, 0, cnt, k=16)
                 ms = c.last_device_ms
-                print(json.dumps({"what": "rnghunt_sweep", "n": n, "cpw": cpw, "candidates": cnt, "ms": ms,
+                print(json.dumps({"what": "rnghunt_sweep", "n": n, "kernel": name, "candidates": cnt, "ms": ms,
                                   "launches": c.last_launches, "cand_per_s": cnt / ms * 1e3,
                                   "stage_counts": [int(v) for v in r["stage_counts"]], "best": r["best"][:4]}), flush=True)
-        c.set_tuning("hunt_cpw", 0)
+            for k in knobs:
+                c.set_tuning(k, 0)
     c.close()
 
 
