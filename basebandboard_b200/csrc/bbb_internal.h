@@ -79,7 +79,7 @@ struct bbb_ctx {
         uint32_t *dev = nullptr;
         size_t bytes = 0;
         uint64_t stamp = 0;
-    } jump_sets[4];
+    } jump_sets[24];               // a chunked host-buffer stream call repeats the same handful of geometries chunk after chunk
     uint64_t jump_stamp = 0;
     HostMat A;                    // dense A
     std::vector<HostMat> Apow2;   // A^(2^i), grown on demand

@@ -272,7 +272,7 @@ static uint32_t *upload_jump_ops(bbb_ctx *c, uint64_t L, uint32_t nbits)
     const uint32_t n = c->n, nw32 = (n + 31) / 32;
     const size_t per = (size_t)n * nw32;
     // a few (L, nbits) geometries recur from call to call (a straight-line launch and its tail):
-    // keep the four most recently used operator sets on the device
+    // keep the most recently used operator sets on the device
     bbb_ctx::JumpSet *slot = &c->jump_sets[0];
     for (auto &js : c->jump_sets) {
         if (js.L == L && js.nbits >= nbits && nbits && js.dev) { js.stamp = ++c->jump_stamp; return js.dev; }

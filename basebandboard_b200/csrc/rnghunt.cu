@@ -364,6 +364,25 @@ __global__ void hunt_front_kernel(FrontParams p)
 // few survivors) goes to global memory.
 // shared: taps[n][CPW+1] words, seq[ceil(2n/32)][CPW] words
 // ---------------------------------------------------------------------------
+// The per-warp tap scratch is rewritten for every group of candidates: keep its lines in L2 (evict_last) so that
+// they are not written back to HBM between two uses.
+__device__ __forceinline__ uint64_t l2_keep_policy()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void st_keep(uint32_t *p, uint32_t v, uint64_t pol)
+{
+    asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(pol) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_keep(const uint32_t *p, uint64_t pol)
+{
+    uint32_t v;
+    asm volatile("ld.global.cg.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol) : "memory");
+    return v;
+}
+
 // ballot of (x & 1) over the warp: the AND and the predicate in ONE LOP3 (its predicate output), then the vote --
 // written out because the compiler spends LOP3 + ISETP on `__ballot_sync(~0u, x & 1)`
 __device__ __forceinline__ uint32_t ballot_odd(uint32_t x)
@@ -498,6 +517,7 @@ hunt_front_pow_kernel(FrontParams p)
     uint32_t *seq = hsm + (size_t)n * RS;
     uint32_t *taps = tap_scratch + (size_t)blockIdx.x * n * 32u;
     const uint32_t ngroups = (p.count + 31u) / 32u;
+    const uint64_t keep_pol = l2_keep_policy();
 
     for (;;) {
         uint32_t g = 0;
@@ -515,7 +535,7 @@ hunt_front_pow_kernel(FrontParams p)
                 const uint32_t cc = col == n ? prev : col;     // empty slot: repeat the previous pick
                 prev = cc;
                 acc |= cc << (8 * k);
-                if (k == 3) { __stcg(taps + row * 32u + lane, acc); acc = 0; }
+                if (k == 3) { st_keep(taps + row * 32u + lane, acc, keep_pol); acc = 0; }
             });
         }
         __syncwarp();
@@ -528,7 +548,7 @@ hunt_front_pow_kernel(FrontParams p)
 #pragma unroll
             for (int j = 0; j < NW; j++) {
                 const uint32_t row = lane + 32u * j;
-                T[j] = row < n ? __ldcg(taps + row * 32u + c) : 0xffffffffu;   // rows >= n: four repeated picks of column 255 ...
+                T[j] = row < n ? ld_keep(taps + row * 32u + c, keep_pol) : 0xffffffffu;   // rows >= n are never used
 #pragma unroll
                 for (int w = 0; w < NW; w++) M[j][w] = 0;
                 if (row < n) {
