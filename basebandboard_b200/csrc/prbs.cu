@@ -738,6 +738,8 @@ int bbb_prbs_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t 
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
     const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 32);   // 4 GiB of sampled int8 noise per pass
+    const int16_t *d_cf = shaper_upload(c, cf);
+    if (!d_cf) return BBB_ECUDA;
     uint32_t rounds = 0;
     for (uint64_t off = 0; off < nbits; off += CH) {
         const uint64_t nb = nbits - off < CH ? nbits - off : CH, nw = nb / 64;
@@ -855,11 +857,15 @@ __device__ __forceinline__ void shaper_emit(const char *Tl, uint32_t win, uint64
 // a bit period are conflict-free whatever the data (a single 4 KB table costs ~3.5 wavefronts per lookup
 // on random patterns, which made shared memory, not HBM, the limit: 4.6 TB/s).  One 1024-thread CTA per SM.
 __global__ void __launch_bounds__(SHAPER_THREADS, SHAPER_CTAS)
-shaper_stream_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t first_bit, uint64_t nbits, ShaperCoef cf,
-                     uint32_t bit_en, const int8_t *__restrict__ g, int32_t noise_var, uint4 *__restrict__ out)
+shaper_stream_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t first_bit, uint64_t nbits,
+                     const int16_t *__restrict__ cfd, uint32_t bit_en, const int8_t *__restrict__ g, int32_t noise_var,
+                     uint4 *__restrict__ out)
 {
     extern __shared__ uint32_t T2[];
     __shared__ uint32_t stage[1024];
+    __shared__ int16_t cfs[64];           // the 64 taps: indexed at run time, so not a by-value parameter (local memory)
+    if (threadIdx.x < 64) cfs[threadIdx.x] = cfd[threadIdx.x];
+    __syncthreads();
     {
         const uint32_t e = threadIdx.x, pp = e >> 8, idx = e & 255u;
         uint32_t pair = 0;
@@ -871,7 +877,7 @@ shaper_stream_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t f
             for (int i = 0; i < 8; i++) {
                 // p >= 4: tap 8i + p - 4 of bit J - i;  p < 4: tap 8i + p + 4 of bit J - 1 - i; pattern bit 7 - i
                 const int k = p >= 4 ? 8 * i + p - 4 : 8 * i + p + 4;
-                const int32_t c = cf.c[k];
+                const int32_t c = cfs[k];
                 a += ((idx >> (7 - i)) & 1u) ? c : -c;
             }
             pair |= ((uint32_t)a & 0xffffu) << (16 * h);
@@ -955,10 +961,14 @@ shaper_stream_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t f
 // tabulates it for the call's `delay` (256 int32, one copy per lane: conflict-free lookups); a thread then takes
 // its 73 window bits from three packed PRBS words and its 64 noise bytes with four 128-bit loads.
 __global__ void __launch_bounds__(256)
-shaped_slicer_err_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t first_bit, uint64_t nwords, ShaperCoef cf,
-                         uint32_t delay, const int8_t *__restrict__ g, int32_t noise_var, uint64_t *__restrict__ err)
+shaped_slicer_err_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64_t first_bit, uint64_t nwords,
+                         const int16_t *__restrict__ cfd, uint32_t delay, const int8_t *__restrict__ g, int32_t noise_var,
+                         uint64_t *__restrict__ err)
 {
     __shared__ int32_t S[256 * 32];
+    __shared__ int16_t cfs[64];           // run-time indexed taps (a by-value struct would be copied to local memory)
+    if (threadIdx.x < 64) cfs[threadIdx.x] = cfd[threadIdx.x];
+    __syncthreads();
     {
         const uint32_t idx = threadIdx.x;         // 256 threads: one pattern each
         int32_t a = 0;
@@ -966,7 +976,7 @@ shaped_slicer_err_kernel(const uint64_t *__restrict__ txw, int64_t origin, int64
         for (int t = 0; t < 8; t++) {
             // delay >= 4: tap 8t + delay - 4 of bit J - t (pattern bit 7 - t of win >> 1); else tap 8t + delay + 4 of bit J - 1 - t
             const int k = delay >= 4 ? 8 * t + (int)delay - 4 : 8 * t + (int)delay + 4;
-            const int32_t c = cf.c[k];
+            const int32_t c = cfs[k];
             a += ((idx >> (7 - t)) & 1u) ? c : -c;
         }
 #pragma unroll
@@ -1060,6 +1070,15 @@ static int shaper_check(bbb_ctx *c, const int16_t *coeff, ShaperCoef &cf)
     return BBB_OK;
 }
 
+// the 64 taps on the device (scratch slot 13): the kernels index them at run time
+static const int16_t *shaper_upload(bbb_ctx *c, const ShaperCoef &cf)
+{
+    int16_t *d = (int16_t *)c->scratch(13, sizeof cf.c);
+    if (!d) return nullptr;
+    if (c->h2d(d, cf.c, sizeof cf.c) != cudaSuccess) { c->cuda_fail(cudaGetLastError(), "upload shaper taps"); return nullptr; }
+    return d;
+}
+
 extern "C" {
 
 int bbb_tx_stream_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits, const int16_t *coeff, uint32_t bit_en,
@@ -1078,6 +1097,8 @@ int bbb_tx_stream_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits
     if ((first_bit + nbits) >> 58) return c->fail(BBB_EINVAL, "bit range too large");
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
+    const int16_t *d_cf = shaper_upload(c, cf);
+    if (!d_cf) return BBB_ECUDA;
     // noise on: 2^29 bits per pass bounds the int8 sample buffer at 4 GiB; noise off: the packed PRBS words
     // are the only intermediate (1/128 of the output), 2^32 bits per pass
     const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (x0 ? (1ull << 29) : (1ull << 32));
@@ -1097,7 +1118,7 @@ int bbb_tx_stream_dev(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t nbits
         const uint64_t want_blocks = (nb + SHAPER_THREADS - 1) / SHAPER_THREADS, max_blocks = (uint64_t)c->sm_count * SHAPER_CTAS;
         BBB_CUDA(c, cudaFuncSetAttribute(shaper_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SHAPER_SMEM));
         shaper_stream_kernel<<<(uint32_t)(want_blocks < max_blocks ? want_blocks : max_blocks), SHAPER_THREADS, SHAPER_SMEM, c->stream>>>(
-            d_tx, origin, (int64_t)(first_bit + off), nb, cf, bit_en, d_g, (int32_t)noise_var, (uint4 *)(out_dev + off * 8));
+            d_tx, origin, (int64_t)(first_bit + off), nb, d_cf, bit_en, d_g, (int32_t)noise_var, (uint4 *)(out_dev + off * 8));
         c->last_launches++;
         BBB_CUDA(c, cudaGetLastError());
     }
@@ -1140,6 +1161,8 @@ int bbb_prbs_shaped_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, ui
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
     const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 32);   // 4 GiB of sampled int8 noise per pass
+    const int16_t *d_cf = shaper_upload(c, cf);
+    if (!d_cf) return BBB_ECUDA;
     uint32_t rounds = 0;
     for (uint64_t off = 0; off < nbits; off += CH) {
         const uint64_t nb = nbits - off < CH ? nbits - off : CH, nw = nb / 64;
@@ -1155,7 +1178,7 @@ int bbb_prbs_shaped_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, ui
         rc = bbb_clt_run_decimated(c, x0, (first_bit + off + 4) * 8, nb, 8u, delay, d_g);
         if (rc) return rc;
         shaped_slicer_err_kernel<<<(uint32_t)((nw + 255) / 256), 256, 0, c->stream>>>(
-            d_tx, origin, (int64_t)(first_bit + off), nw, cf, delay, d_g, (int32_t)noise_var, d_err);
+            d_tx, origin, (int64_t)(first_bit + off), nw, d_cf, delay, d_g, (int32_t)noise_var, d_err);
         c->last_launches++;
         BBB_CUDA(c, cudaGetLastError());
         rc = detect_impl(c, k, first_bit + off, nb, 0, 0, d_err, &d0, ctr);

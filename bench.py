@@ -139,6 +139,17 @@ def run_reference(args, rank, world):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if not args.no_secondary:
+        # the metric's second half on the same arm: the oracle port of the rnghunt worker loop, all host cores
+        rate, cnt, counts = cpu_rnghunt_rate(min(args.cpu_seconds, 8.0), cores)
+        line["secondary"] = {"rnghunt": {
+            "metric": "rnghunt_candidates_per_s", "value": rate, "unit": "candidates/s", "higher_is_better": True,
+            "config": {"workload": "rnghunt sweep n=%d, seed %d (BASELINE.json configs[3]); bounded sample of the fixed "
+                                   "candidate set [0, 2^%d)" % (HUNT_N, HUNT_SEED, args.hunt_log2)},
+            "cpu_baseline": {"value": rate, "unit": "candidates/s", "cores": cores, "kind": "port",
+                             "sample": "candidates [0, %d) (oracle/rnghunt_ref.c, %d threads), stage counts %s"
+                                       % (cnt, cores, counts)},
+            "e2e": {"value": rate, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}}
     emit_json(line)
 
 
@@ -157,13 +168,17 @@ def workload_config(args, world):
 HUNT_N, HUNT_SEED, HUNT_LOG2, HUNT_K = 192, 1, 24, 16     # BASELINE.json configs[3] as SURVEY.md 8d restates it
 
 
-def hunt_alg_lop3_per_candidate(n):
-    """Algorithmic work of the sweep's dominant kernel (hunt_front_warp_kernel): 2n clocks of x' = A.x
-    (binary_matrix.rs:68-76), each clock = n rows x ceil(n/32) mask words, one LOP3 ((W & M) ^ acc) per word.
-    (The same clocks as sparse gathers: 2n x 31n/8 tap reads -- 286 k at n = 192 -- the form the thread-per-
-    candidate kernel of round 1 used and lost on, shared-memory bound.)"""
+def hunt_alg_lop3_per_candidate(n, k=8):
+    """Algorithmic ALU work of the sweep's dominant kernel (hunt_front_pow_kernel) per candidate, as LOP3-equivalent
+    thread-instructions: the 2n clocks of x' = A.x (binary_matrix.rs:68-76) are applied K at a time through A^K kept
+    as dense row masks -- (2n/K) passes of (NW+1) row groups x (NW mask LOP3 + 1 parity predicate) per lane -- after
+    K-1 sparse products A.P that build A^K (4 taps x NW word-XORs per row).  Candidate generation, Berlekamp-Massey,
+    votes and addressing are NOT counted.  (The same clocks as one-at-a-time sparse gathers, the round-1
+    formulation: 2n x 31n/8 = 286 k byte gathers at n = 192.)"""
     nw = (n + 31) // 32
-    return 2 * n * nw * 32 * nw
+    passes = -(-2 * n // k) * (nw + 1) * (nw + 1)
+    powers = (k - 1) * nw * 4 * nw
+    return 32 * (passes + powers)
 
 
 def crc_u64(words):
@@ -252,13 +267,17 @@ def run_rnghunt_leg(args, ctx, rank, world, local_rank, lop3_peak, barrier):
         "e2e": {"value": total / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "api": "bbb_rnghunt_sweep per rank + merge (host scalars in, host ranking out)"},
         "gpu_launches": launches,
-        "roofline": {"bound": "alu", "kernel": "hunt_front_warp", "achieved": ach, "peak": lop3_peak / 1e12,
+        "roofline": {"bound": "alu", "achieved": ach, "peak": lop3_peak / 1e12,
                      "unit": "T thread-instr/s (LOP3-equivalent)", "frac": ach / (lop3_peak / 1e12), "traffic": None,
                      "launch_ms_per_2p20": sweep_ms / max(1.0, total / world / (1 << 20)),
-                     "note": "algorithmic work = 2n clocks x n rows x ceil(n/32) mask words, one LOP3 each = %d "
-                             "thread-instr per candidate (binary_matrix.rs:68-76); parity, ballots, candidate "
-                             "generation, Berlekamp-Massey and the primitivity stage are not counted; peak = LOP3 "
-                             "issue rate measured live (bbb_measure_lop3_peak); HBM traffic ~0" % alg},
+                     "kernel": "hunt_front_pow<6,8>",
+                     "alu_pipe_busy_ncu": 0.83,
+                     "note": "algorithmic work = (2n/8) passes of A^8 over 7 row groups x (6 mask LOP3 + 1 parity predicate) "
+                             "+ 7 sparse products A.P (4 taps x 6 word-XORs per row) = %d thread-instr per candidate "
+                             "(binary_matrix.rs:68-76); candidate generation (binary_matrix.rs:81-101), Berlekamp-Massey, "
+                             "votes and the primitivity stage are NOT counted, which is why frac is far below the ALU-pipe "
+                             "utilisation ncu reports for the kernel (83 %%, profiles/r2_rnghunt_pow8_ncu_full.txt); peak = "
+                             "LOP3 issue rate measured live (bbb_measure_lop3_peak); HBM traffic ~0" % alg},
         "result_check": {"best": [int(b) for b in res["r"]["best"]],
                          "stage_counts": [int(v) for v in res["r"]["stage_counts"]]},
     }
@@ -551,18 +570,14 @@ def run_secondary(args, ctx, rank, world, local_rank):
             line["result_check"] = dict(extra["ctr"], rounds=extra["rounds"], runs=extra["runs"],
                                         final_state=list(extra["final"]), counters="all-reduced over the ranks")
         if w == "rnghunt":
-            # dominant kernel hunt_front: one shared-memory gather per tap per clock (2n clocks per candidate)
-            from basebandboard_b200 import recurrences as _rec
-            n_ = args.hunt_n
-            taps_per_cand = 2.0 * n_ * (n_ * 31.0 / 8.0)          # row weights [3,4,4,4,4,4,4,4]: 31/8 taps per row
-            sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
-            lsu_peak = sm * 32 * (clocks.get("sm_mhz") or 1965) * 1e6 / 1e12
-            ach = value / world * taps_per_cand / 1e12
-            line["roofline"] = {"bound": "lsu", "kernel": "hunt_front", "achieved": ach, "peak": lsu_peak,
-                                "unit": "T shared-memory lane-loads/s", "frac": ach / lsu_peak, "traffic": None,
-                                "note": "algorithmic work = 2n clocks x 31n/8 tap gathers per candidate (binary_matrix.rs:68-76); "
-                                        "peak = one 32-lane LDS per SM per clock at the sampled SM clock; stores, "
-                                        "Berlekamp-Massey and the primitivity stage are not counted as algorithmic"}
+            lop3 = max(ctx.measure_lop3_peak() for _ in range(3)) / 1e12
+            alg = hunt_alg_lop3_per_candidate(args.hunt_n)
+            ach = value / world * alg / 1e12
+            line["roofline"] = {"bound": "alu", "kernel": "hunt_front_pow", "achieved": ach, "peak": lop3,
+                                "unit": "T thread-instr/s (LOP3-equivalent)", "frac": ach / lop3, "traffic": None,
+                                "note": "algorithmic work = (2n/8) passes of A^8 as dense row masks + 7 sparse products A.P = %d "
+                                        "thread-instr per candidate (see hunt_alg_lop3_per_candidate); generation, "
+                                        "Berlekamp-Massey, votes and the primitivity stage not counted" % alg}
         if "res" in extra:
             line["result_check"] = {"best": extra["res"]["best"],
                                     "stage_counts": [int(v) for v in extra["res"]["stage_counts"]]}
