@@ -738,8 +738,6 @@ int bbb_prbs_slicer_detect(bbb_ctx *c, uint32_t k, uint64_t first_bit, uint64_t 
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
     const uint64_t CH = c->tune_slicer_chunk_bits ? c->tune_slicer_chunk_bits : (1ull << 32);   // 4 GiB of sampled int8 noise per pass
-    const int16_t *d_cf = shaper_upload(c, cf);
-    if (!d_cf) return BBB_ECUDA;
     uint32_t rounds = 0;
     for (uint64_t off = 0; off < nbits; off += CH) {
         const uint64_t nb = nbits - off < CH ? nbits - off : CH, nw = nb / 64;
