@@ -29,3 +29,10 @@ ctx.tx_stream(31, 1 << 29, coeff, first_bit=0, dev_ptr=buf.data_ptr())
 ctx.sync()
 print("tx_stream 2^29 bits %.3f ms = %.1f GB/s" % (ctx.last_device_ms, (1 << 33) / ctx.last_device_ms * 1e-6))
 ctx.close()
+ctx = lib.Context(0)
+ctx.lutopt_load_shipped(256)
+wbuf = torch.empty((1 << 26) * 4, dtype=torch.int64, device="cuda")
+ctx.lutopt_stream_dev(1, 0, 1 << 26, wbuf.data_ptr())
+ctx.sync()
+print("lutopt_stream 2^26 steps %.3f ms = %.1f GB/s [%s]" % (ctx.last_device_ms, (1 << 31) / ctx.last_device_ms * 1e-6, ctx.last_kernel))
+ctx.close()
