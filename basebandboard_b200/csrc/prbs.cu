@@ -1068,10 +1068,10 @@ static int shaper_check(bbb_ctx *c, const int16_t *coeff, ShaperCoef &cf)
     return BBB_OK;
 }
 
-// the 64 taps on the device (scratch slot 13): the kernels index them at run time
+// the 64 taps on the device (scratch slot 14): the kernels index them at run time
 static const int16_t *shaper_upload(bbb_ctx *c, const ShaperCoef &cf)
 {
-    int16_t *d = (int16_t *)c->scratch(13, sizeof cf.c);
+    int16_t *d = (int16_t *)c->scratch(14, sizeof cf.c);
     if (!d) return nullptr;
     if (c->h2d(d, cf.c, sizeof cf.c) != cudaSuccess) { c->cuda_fail(cudaGetLastError(), "upload shaper taps"); return nullptr; }
     return d;
