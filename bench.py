@@ -323,6 +323,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
             if "b" not in host:  # caller-owned buffer, touched once (a fresh calloc page-faults on first write)
                 import numpy as np
                 host["b"] = np.ones(n // 64, dtype=np.uint64)
+                ctx.prbs_stream(args.k, n, first_bit=first, out=host["b"])   # untimed: the ctx allocates its staging buffers
                 return None
             ctx.prbs_stream(args.k, n, first_bit=first, out=host["b"])
             return n, ctx.last_h2d_bytes, ctx.last_d2h_bytes
@@ -401,6 +402,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
             if "b" not in host:
                 import numpy as np
                 host["b"] = np.ones(n * 8, dtype=np.int16)
+                ctx.tx_stream(args.k, n, coeff, first_bit=first, out=host["b"])
                 return None
             ctx.tx_stream(args.k, n, coeff, first_bit=first, out=host["b"])
             return n * 16, ctx.last_h2d_bytes, ctx.last_d2h_bytes
@@ -424,6 +426,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
             if "b" not in host:
                 import numpy as np
                 host["b"] = np.ones(n * 4, dtype=np.uint64)
+                ctx.lutopt_stream(1, first, n, out=host["b"])
                 return None
             ctx.lutopt_stream(1, first, n, out=host["b"])
             return n * 32, ctx.last_h2d_bytes, ctx.last_d2h_bytes
@@ -447,6 +450,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
             if "b" not in host:
                 import numpy as np
                 host["b"] = np.ones(n, dtype=np.int8 if eb == 1 else np.int16)
+                ctx.clt_stream(1, first, n, model=0, noise_var=None if eb == 1 else args.noise_var_stream, out=host["b"])
                 return None
             ctx.clt_stream(1, first, n, model=0, noise_var=None if eb == 1 else args.noise_var_stream, out=host["b"])
             return n, ctx.last_h2d_bytes, ctx.last_d2h_bytes
