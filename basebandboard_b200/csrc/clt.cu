@@ -256,6 +256,7 @@ static int launch_seed(bbb_ctx *c, const uint32_t *dJ, const SeedStart &xs, uint
 // clt_spec.cu
 int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only);
 int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c, int kind);
+int bbb_clt_spec_words_streams_per_block(const bbb_ctx *c);
 int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model, const uint32_t *planes,
                         unsigned long long *hist);
 int bbb_clt_spec_stream_ok(const bbb_ctx *c, int kind);
@@ -362,6 +363,7 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
     else if (d_out16 && !d_hist && !d_out8 && !d_out_words32 && ((uintptr_t)d_out16 & 15) == 0) kind = 3;
     uint64_t spb = 0;
     if (kind == 0) spb = (uint64_t)bbb_clt_spec_streams_per_block(c, true);
+    else if (kind == 2 && bbb_clt_spec_stream_ok(c, kind)) spb = (uint64_t)bbb_clt_spec_words_streams_per_block(c);
     else if (kind > 0 && bbb_clt_spec_stream_ok(c, kind)) spb = (uint64_t)bbb_clt_spec_streams_per_block(c, true);
 
     uint64_t done = 0;

@@ -242,6 +242,13 @@ int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only)
     return CLT256_B * 32;
 }
 
+// the raw-word kernel runs 192-thread CTAs (clt256_words3_kernel) unless a knob selects an older variant
+int bbb_clt_spec_words_streams_per_block(const bbb_ctx *c)
+{
+    if (c->shipped != 256 || c->tune_no_spec) return 0;
+    return (c->tune_spec_variant != 1 && !c->tune_words_b128) ? 192 * 32 : CLT256_B * 32;
+}
+
 // Launches the fused kernel on `blocks` CTAs; planes = [256][T] bit-sliced states whose CLT value is
 // the first sample of each stream, T = blocks * 128.
 int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model, const uint32_t *planes,
@@ -662,6 +669,66 @@ clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
     }
 }
 
+// ---------------------------------------------------------------------------
+// clt256_words3_kernel: the same clock and transposes with SIX warps per SM instead of four.  ncu on words2 shows
+// neither pipe busy (ALU 34 %, LSU 36 %): with one warp per scheduler a warp's store phase and its ALU phase never
+// overlap.  192 threads need 114 KB of state, which leaves room for HALF a clock of staging (4 of the 8 words of
+// every stream: 96 KB), so a clock is flushed in two passes of one 16-byte piece per stream; the pieces of a
+// line meet in L2 (evict_last), as the four clocks of a line already do.  A thread reads back only its own
+// staged words, so no warp synchronisation is needed.  The generated body is re-instantiated with B = 192.
+// ---------------------------------------------------------------------------
+#pragma push_macro("CLT256V2_B")
+#pragma push_macro("CLT256V2_W_EMIT")
+#undef CLT256V2_B
+#undef CLT256V2_W_EMIT
+#define CLT256V2_B 192
+#define CLT256V3W_STAGE_WORDS (32 * 4 * 192)
+#define CLT256V3W_STATE_BYTES (CLT256V2_NSLOTS * 192 * 4)
+#define CLT256V3W_SMEM (CLT256V3W_STATE_BYTES + CLT256V3W_STAGE_WORDS * 4)
+
+#define CLT256V2_W_EMIT(w, r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18, r19, \
+                        r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31)                                  \
+    {                                                                                                                \
+        uint32_t tw[32] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18,       \
+                           r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31};                          \
+        transpose32_fast(tw);                                                                                        \
+        _Pragma("unroll") for (int j = 0; j < 32; j++)                                                               \
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(stage_a + (uint32_t)((j * 4 + ((w) & 3)) * 192 * 4)), "r"(tw[j])); \
+        if (((w) & 3) == 3) {                                                                                        \
+            uint32_t *const o32 = outp + (size_t)it * 8u + ((w) >> 2) * 4u;                                          \
+            _Pragma("unroll 8") for (int j = 0; j < 32; j++) {                                                       \
+                uint32_t v[4];                                                                                       \
+                _Pragma("unroll") for (int i = 0; i < 4; i++)                                                        \
+                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[i]) : "r"(stage_a + (uint32_t)((j * 4 + i) * 192 * 4))); \
+                CLT256V2W_STORE((uint4 *)(o32 + (size_t)j * L * 8u), make_uint4(v[0], v[1], v[2], v[3]));             \
+            }                                                                                                        \
+        }                                                                                                            \
+    }
+
+__global__ void __launch_bounds__(192, 1)
+clt256_words3_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * 192u + tid;
+    uint32_t *const st = (uint32_t *)smem4 + tid;
+    for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * 192u] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+    const uint32_t stage_a = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V3W_STATE_BYTES) + tid * 4u;
+    uint32_t *const outp = out + (size_t)t * 32u * L * 8u;   // stream j, clock it: outp + (j*L + it)*8
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_W_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_W_BODY
+    }
+}
+#pragma pop_macro("CLT256V2_W_EMIT")
+#pragma pop_macro("CLT256V2_B")
+
 // kind: 1 = int8 samples, 2 = raw words, 3 = int16 scaled samples
 int bbb_clt_spec_stream_ok(const bbb_ctx *c, int kind)
 {
@@ -692,6 +759,11 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
                                                                              (int32_t)noise_var);
         c->last_kernel = "clt256_s16";
+    } else if (c->tune_spec_variant != 1 && !c->tune_words_b128) {
+        static_assert(CLT256V3W_SMEM <= 227 * 1024, "shared memory budget");
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_words3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V3W_SMEM));
+        clt256_words3_kernel<<<blocks, 192, CLT256V3W_SMEM, c->stream>>>(planes, blocks * 192, L, (uint32_t *)out);
+        c->last_kernel = "clt256_words3";
     } else if (c->tune_spec_variant != 1) {
         static_assert(CLT256V2W_SMEM <= 227 * 1024, "shared memory budget");
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2W_SMEM));

@@ -43,11 +43,12 @@ def main():
     if "streams" in what:
         c.lutopt_load_shipped(256)
         for name, count, bytes_per in (("clt_stream_i8", 1 << 33, 1), ("clt_stream_i16", 1 << 32, 2),
-                                       ("lutopt_stream", 1 << 28, 32)):
+                                       ("lutopt_stream", 1 << 28, 32), ("lutopt_stream_b128", 1 << 28, 32)):
+            c.set_tuning("words_b128", 1 if name.endswith("b128") else 0)
             buf = torch.empty(count * bytes_per, dtype=torch.uint8, device="cuda")
             ms = []
             for _ in range(3):
-                if name == "lutopt_stream":
+                if name.startswith("lutopt_stream"):
                     c.lutopt_stream_dev(1, 0, count, buf.data_ptr())
                 else:
                     c.clt_stream_dev(1, 0, count, 0, 8 if bytes_per == 2 else 1, buf.data_ptr(), bytes_per)
