@@ -242,11 +242,11 @@ int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only)
     return CLT256_B * 32;
 }
 
-// the raw-word kernel runs 192-thread CTAs (clt256_words3_kernel) unless a knob selects an older variant
+// the raw-word kernel runs 128-thread CTAs; the knob "words_b192" selects the 192-thread experiment (clt256_words3_kernel)
 int bbb_clt_spec_words_streams_per_block(const bbb_ctx *c)
 {
     if (c->shipped != 256 || c->tune_no_spec) return 0;
-    return (c->tune_spec_variant != 1 && !c->tune_words_b128) ? 192 * 32 : CLT256_B * 32;
+    return (c->tune_spec_variant != 1 && c->tune_words_b192) ? 192 * 32 : CLT256_B * 32;
 }
 
 // Launches the fused kernel on `blocks` CTAs; planes = [256][T] bit-sliced states whose CLT value is
@@ -670,12 +670,13 @@ clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 }
 
 // ---------------------------------------------------------------------------
-// clt256_words3_kernel: the same clock and transposes with SIX warps per SM instead of four.  ncu on words2 shows
-// neither pipe busy (ALU 34 %, LSU 36 %): with one warp per scheduler a warp's store phase and its ALU phase never
-// overlap.  192 threads need 114 KB of state, which leaves room for HALF a clock of staging (4 of the 8 words of
-// every stream: 96 KB), so a clock is flushed in two passes of one 16-byte piece per stream; the pieces of a
-// line meet in L2 (evict_last), as the four clocks of a line already do.  A thread reads back only its own
-// staged words, so no warp synchronisation is needed.  The generated body is re-instantiated with B = 192.
+// clt256_words3_kernel (EXPERIMENT, knob "words_b192"; measured and rejected): the same clock and transposes with
+// SIX warps per SM instead of four.  ncu on words2 shows neither pipe busy (ALU 34 %, LSU 36 %), so more warps
+// looked like the fix; but 192 threads need 114 KB of state, which leaves room for only HALF a clock of staging
+// (4 of the 8 words of every stream: 96 KB), so a clock leaves in two passes of one 16-byte piece per stream.
+// Result at 2^28 steps: 494 GB/s against 1658 GB/s for words2 -- half-sector stores cost far more than the extra
+// warps give, even with the pieces meeting in L2 (evict_last).  Complete 32-byte sectors per store are what matters.
+// The generated body is re-instantiated with B = 192.
 // ---------------------------------------------------------------------------
 #pragma push_macro("CLT256V2_B")
 #pragma push_macro("CLT256V2_W_EMIT")
@@ -759,7 +760,7 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
                                                                              (int32_t)noise_var);
         c->last_kernel = "clt256_s16";
-    } else if (c->tune_spec_variant != 1 && !c->tune_words_b128) {
+    } else if (c->tune_spec_variant != 1 && c->tune_words_b192) {
         static_assert(CLT256V3W_SMEM <= 227 * 1024, "shared memory budget");
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V3W_SMEM));
         clt256_words3_kernel<<<blocks, 192, CLT256V3W_SMEM, c->stream>>>(planes, blocks * 192, L, (uint32_t *)out);

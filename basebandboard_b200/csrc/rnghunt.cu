@@ -125,6 +125,71 @@ __device__ __forceinline__ void hunt_generate(uint32_t n, uint64_t seed, uint64_
     }
 }
 
+// The same generator with less bookkeeping (n <= 256; used by hunt_front_pow_kernel, where generation is 40 % of the
+// instructions).  Within one pass over the columns "raised" = ALL \ minm, so no second mask is kept, and a column
+// picked in this row leaves minm at once, so "not yet used in this row" only matters after minm has been refilled
+// in the middle of a row (once in ~50 rows): then the row's earlier picks are excluded through `excl`, rebuilt from
+// the (at most four) picks.  The number of candidates is counted, not re-derived by popcounts.  Draw for draw the
+// same sequence as hunt_generate (the GPU tests compare the kernels that use either with the oracle).
+template <int NW, typename Put>
+__device__ __forceinline__ void hunt_generate_fast(uint32_t n, uint64_t seed, uint64_t cand, Put put)
+{
+    HuntRng rng;
+    rng.init(seed, cand);
+    uint32_t minm[NW], excl[NW];
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+        const uint32_t lo = (uint32_t)w * 32u;
+        minm[w] = n >= lo + 32 ? 0xffffffffu : (n > lo ? (1u << (n - lo)) - 1u : 0u);
+        excl[w] = 0;
+    }
+    uint32_t cntmin = n;
+    for (uint32_t row = 0; row < n; row++) {
+        const uint32_t weight = rng.draw(8) == 0 ? 3u : 4u;   // rowweights[..] = [3,4,4,4,4,4,4,4]
+        uint32_t pb = 0, cols = 0;                            // picks of this row made before a refill; the picks
+        for (uint32_t k = 0; k < 4; k++) {
+            const uint32_t tot = cntmin - pb;                 // |minm \ row picks|
+            if (k >= weight || tot == 0) { put(row, k, n); continue; }
+            const uint32_t r = rng.draw(tot);
+            uint32_t word = minm[0] & ~excl[0], wi = 0, base = 0, s = __popc(word);
+#pragma unroll
+            for (int w = 1; w < NW; w++) {
+                const uint32_t a = minm[w] & ~excl[w];
+                const bool ge = r >= s;
+                wi = ge ? (uint32_t)w : wi;
+                base = ge ? s : base;
+                word = ge ? a : word;
+                s += __popc(a);
+            }
+            const uint32_t bit = nth_set_bit(word, r - base);
+            const uint32_t col = wi * 32u + bit, m = 1u << bit;
+            put(row, k, col);
+#pragma unroll
+            for (int w = 0; w < NW; w++) minm[w] &= ~((uint32_t)w == wi ? m : 0u);
+            cols |= col << (8 * k);
+            if (--cntmin == 0) {                              // every column has been raised: the next level starts
+#pragma unroll
+                for (int w = 0; w < NW; w++) {
+                    const uint32_t lo = (uint32_t)w * 32u;
+                    minm[w] = n >= lo + 32 ? 0xffffffffu : (n > lo ? (1u << (n - lo)) - 1u : 0u);
+                    excl[w] = 0;
+                }
+                cntmin = n;
+                pb = k + 1;
+                for (uint32_t q = 0; q <= k; q++) {
+                    const uint32_t c = (cols >> (8 * q)) & 0xffu;
+#pragma unroll
+                    for (int w = 0; w < NW; w++) excl[w] |= (c >> 5) == (uint32_t)w ? 1u << (c & 31u) : 0u;
+                }
+            }
+        }
+        if (pb) {
+#pragma unroll
+            for (int w = 0; w < NW; w++) excl[w] = 0;
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------
 // online Berlekamp-Massey over GF(2) (berlekamp_massey.rs:5-31 fed u[t] = recur output t)
 //   c, b: connection polynomials, bit j = coefficient c_j (LSB-first words); bsh = b * x^(t-m)
@@ -531,7 +596,7 @@ hunt_front_pow_kernel(FrontParams p)
         if (lane < ncand) {
             const uint64_t cand = p.first + (uint64_t)(slot0 + lane) * p.stride;
             uint32_t acc = 0, prev = 0;
-            hunt_generate<NW>(n, p.seed, cand, [&](uint32_t row, uint32_t k, uint32_t col) {
+            hunt_generate_fast<NW>(n, p.seed, cand, [&](uint32_t row, uint32_t k, uint32_t col) {
                 const uint32_t cc = col == n ? prev : col;     // empty slot: repeat the previous pick
                 prev = cc;
                 acc |= cc << (8 * k);

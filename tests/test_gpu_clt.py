@@ -275,11 +275,11 @@ def test_decimated_stream_equals_full_stream_large(ctx):
 @pytest.mark.parametrize("variant", [1, 2, 3])
 @pytest.mark.parametrize("blocks,min_steps,count,first", [(1, 8, 6144 * 9 + 5, 0), (2, 8, 2 * 6144 * 11 + 3, (1 << 35) + 1)])
 def test_spec256_word_stream_matches_oracle(ctx, orc, blocks, min_steps, count, first, variant):
-    """raw URNG words: two-pass clt256_words (1), one-pass clt256_words2 with 128-thread CTAs (2) and the
-    192-thread clt256_words3 the product path uses (3), each + the data-driven tail, == oracle"""
+    """raw URNG words: two-pass clt256_words (1), one-pass clt256_words2 (2, the product path) and the 192-thread
+    experiment clt256_words3 (3), each + the data-driven tail, == oracle"""
     ctx.lutopt_load_shipped(256)
     ctx.set_tuning("clt_spec_variant", 1 if variant == 1 else 2)
-    ctx.set_tuning("words_b128", 1 if variant == 2 else 0)
+    ctx.set_tuning("words_b192", 1 if variant == 3 else 0)
     ctx.set_tuning("clt_spec_min_steps", min_steps)
     ctx.set_tuning("clt_spec_max_blocks", blocks)
     try:
@@ -291,7 +291,7 @@ def test_spec256_word_stream_matches_oracle(ctx, orc, blocks, min_steps, count, 
         ctx.set_tuning("clt_spec_min_steps", 512)
         ctx.set_tuning("clt_spec_max_blocks", 0)
         ctx.set_tuning("clt_spec_variant", 2)
-        ctx.set_tuning("words_b128", 0)
+        ctx.set_tuning("words_b192", 0)
 
 
 def test_spec256_streams_equal_generic_large(ctx):
