@@ -88,6 +88,10 @@ int32_t orc_clt(uint32_t n, const uint64_t *x, int model)
     uint32_t logn = 0;
     while ((1u << logn) < n) logn++;
     for (uint32_t i = 0; i < n; i++) lvl[i] = (int16_t)getbit(x, i);
+    /* CLTGRNG needs n a power of two (rng.py:73-74).  A caller that only wants the LUTOPT words of another n (192)
+     * still passes through here: pad with zeros so that the tree reads defined values and |g| <= n/2 holds
+     * (uninitialised padding used to index the histogram out of bounds). */
+    for (uint32_t i = n; i < (1u << logn); i++) lvl[i] = 0;
     for (uint32_t level = 0; level < logn; level++) {
         uint32_t level_n = 1u << (logn - level);
         for (uint32_t pair = 0; pair < level_n; pair += 2) lvl[pair / 2] = (int16_t)(lvl[pair] - lvl[pair + 1]);
