@@ -303,6 +303,7 @@ def run_secondary(args, ctx, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sm_count = torch.cuda.get_device_properties(local_rank).multi_processor_count
     hbm_peak = None
     try:
         hbm_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
@@ -515,18 +516,18 @@ def run_secondary(args, ctx, rank, world, local_rank):
             ach = units / (dev_ms / args.steps * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "kernel": "shaper_stream", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                                 "frac": ach / hbm_peak,
-                                "traffic": 8617702000 if args.log2_bits == 36 else None,
-                                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one shaper_stream_kernel launch at "
-                                                "2^29 bits (ncu --set full, profiles/r1_shaper_stream_ncu_full.txt): 8.55 GB written "
-                                                "for 8.59 GB of TX words, 68 MB read (the packed PRBS words)",
+                                "traffic": 8597517000 if (args.log2_bits == 36 and not args.tune and sm_count == 148) else None,
+                                "traffic_note": "NOT re-measured in this run (null under --tune, another size or SM count): dram__bytes_read.sum + dram__bytes_write.sum of one shaper_stream_kernel launch at "
+                                                "2^29 bits (ncu --set full, profiles/r2_tx_words_kernels_ncu_full.txt): 8.53 GB written "
+                                                "for 8.59 GB of TX words, 67 MB read (the packed PRBS words)",
                                 "note": "algorithmic bytes = 16 B written per PRBS bit (8 int16 TX words); "
                                 "peak = measured copy bandwidth (MEASURED_PEAKS.json), per GPU"}
         if w == "prbs_stream" and hbm_peak:
             ach = units / 8 / (dev_ms / args.steps * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "kernel": "prbs_stream", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                                 "frac": ach / hbm_peak,
-                                "traffic": 8529677576 if (args.log2_bits == 36 and args.k == 31) else None,
-                                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of the 2^36-bit prbs_stream_kernel "
+                                "traffic": 8529677576 if (args.log2_bits == 36 and args.k == 31 and not args.tune and sm_count == 148) else None,
+                                "traffic_note": "NOT re-measured in this run (null under --tune, another size, k or SM count): dram__bytes_read.sum + dram__bytes_write.sum of the 2^36-bit prbs_stream_kernel "
                                                 "launch (ncu --set full, profiles/r1_prbs_stream_ncu_full.txt): 8.53 GB written "
                                                 "for 8.59 GB of packed bits (the last lines are still in L2 at kernel end), 0.1 MB read",
                                 "note": "algorithmic bytes = 1/8 B per PRBS bit; peak = measured copy bandwidth "
@@ -535,7 +536,9 @@ def run_secondary(args, ctx, rank, world, local_rank):
             ach = units / (dev_ms / args.steps * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "kernel": ctx.last_kernel, "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                                 "frac": ach / hbm_peak, "traffic": None,
-                                "traffic_note": "see profiles/ for the ncu --set full capture of this kernel (dram bytes per launch)",
+                                "traffic_note": "ncu --set full of clt256_words2_kernel at 2^26 steps (profiles/r2_tx_words_kernels_ncu_full.txt): "
+                                                "2.095 GB written + 0.017 GB read for 2.147 GB of output = 0.98x the algorithmic bytes; "
+                                                "not re-measured at this size",
                                 "note": "algorithmic bytes = 32 B written per LUTOPT step (the 256-bit state, rng.py:27); "
                                         "peak = measured copy bandwidth (MEASURED_PEAKS.json), per GPU"}
         if w == "clt_stream":
