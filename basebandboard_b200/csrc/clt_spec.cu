@@ -598,8 +598,24 @@ clt256_words_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
         uint32_t tw[32] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18,       \
                            r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31};                          \
         transpose32_fast(tw);                                                                                        \
+        if ((w) == 0) __syncwarp();      /* every lane has drained the previous clock's words */                       \
         _Pragma("unroll") for (int j = 0; j < 32; j++)                                                               \
             asm volatile("st.shared.u32 [%0], %1;" ::"r"(((w) < 4 ? stage_a : stage_b) + (uint32_t)((j * 8 + (w)) * CLT256V2_B * 4)), "r"(tw[j])); \
+    }
+
+// One stream index j of the PREVIOUS clock leaves the stage (the generator places 32 of these between the steps of
+// the clock, so the stores drain behind the clock's ALU work instead of stalling the warp after the transposes:
+// ncu on the unpipelined kernel showed 1.25 long-scoreboard stalls per issued instruction and 26 % issue activity).
+#define CLT256V2_W_DRAIN(j)                                                                                          \
+    if (it != 0u) {                                                                                                  \
+        uint32_t v[8];                                                                                               \
+        _Pragma("unroll") for (int i = 0; i < 4; i++) {                                                              \
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[i]) : "r"(rd0 + (uint32_t)(((j) * 8 + i) * CLT256V2_B * 4)));     \
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[4 + i]) : "r"(rd1 + (uint32_t)(((j) * 8 + i) * CLT256V2_B * 4))); \
+        }                                                                                                            \
+        const size_t off = ((size_t)(j) * L + (it - 1u)) * 8u;                                                       \
+        CLT256V2W_STORE((uint4 *)(op0 + off), make_uint4(v[0], v[1], v[2], v[3]));                                   \
+        CLT256V2W_STORE((uint4 *)(op1 + off), make_uint4(v[4], v[5], v[6], v[7]));                                   \
     }
 
 // Store policy of the final 16-byte pieces.  A stream's 128-byte line is completed by four consecutive clocks
@@ -649,23 +665,16 @@ clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 
 #pragma unroll 1
     for (uint32_t it = 0; it < L; it++) {
+        __syncwarp();                    // the stage holds clock it-1 of every lane's threads
 #define CLT256V2_SECTION_W_BODY
 #include "clt256_v2_gen.inc"
 #undef CLT256V2_SECTION_W_BODY
-        __syncwarp();
+    }
+    __syncwarp();
+    {                                    // the last clock's words
+        const uint32_t it = L;
 #pragma unroll 4
-        for (int j = 0; j < 32; j++) {
-            uint32_t v[8];
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[i]) : "r"(rd0 + (uint32_t)((j * 8 + i) * CLT256V2_B * 4)));
-                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[4 + i]) : "r"(rd1 + (uint32_t)((j * 8 + i) * CLT256V2_B * 4)));
-            }
-            const size_t off = ((size_t)j * L + it) * 8u;
-            CLT256V2W_STORE((uint4 *)(op0 + off), make_uint4(v[0], v[1], v[2], v[3]));
-            CLT256V2W_STORE((uint4 *)(op1 + off), make_uint4(v[4], v[5], v[6], v[7]));
-        }
-        __syncwarp();
+        for (int j = 0; j < 32; j++) { CLT256V2_W_DRAIN(j) }
     }
 }
 
@@ -682,6 +691,9 @@ clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #pragma push_macro("CLT256V2_W_EMIT")
 #undef CLT256V2_B
 #undef CLT256V2_W_EMIT
+#pragma push_macro("CLT256V2_W_DRAIN")
+#undef CLT256V2_W_DRAIN
+#define CLT256V2_W_DRAIN(j)
 #define CLT256V2_B 192
 #define CLT256V3W_STAGE_WORDS (32 * 4 * 192)
 #define CLT256V3W_STATE_BYTES (CLT256V2_NSLOTS * 192 * 4)
@@ -727,6 +739,7 @@ clt256_words3_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #undef CLT256V2_SECTION_W_BODY
     }
 }
+#pragma pop_macro("CLT256V2_W_DRAIN")
 #pragma pop_macro("CLT256V2_W_EMIT")
 #pragma pop_macro("CLT256V2_B")
 

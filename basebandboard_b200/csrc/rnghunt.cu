@@ -1303,7 +1303,13 @@ static int hunt_sweep(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uin
     c->last_kernel = "rnghunt_sweep";
     const uint32_t nwp = (n + 31) / 32 + 1;
     const bool want_polys = poly_words || weights;
-    const uint64_t batch_max = c->tune_hunt_batch ? c->tune_hunt_batch : (1u << 20);
+    // batches of 2^20 candidates, but at least four of them per call where the call is long enough (a rank's share of a
+    // strong-scaled sweep): the back end of a batch hides behind the front kernel of the next one
+    uint64_t batch_max = c->tune_hunt_batch ? c->tune_hunt_batch : (1u << 20);
+    if (!c->tune_hunt_batch && count < 4 * batch_max) {
+        batch_max = ((count + 3) / 4 + 4095) & ~(uint64_t)4095;
+        if (batch_max < (1u << 16)) batch_max = 1u << 16;
+    }
     const uint32_t cap = (uint32_t)(count < batch_max ? (count ? count : 1) : batch_max);
     HuntShared sh;
     HuntSlot slots[2];

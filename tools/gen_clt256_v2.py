@@ -175,6 +175,10 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
         for b in rows[r]:
             taps_at[pos[b]].append(r)
     hooks = rmw_hooks_v2() if kind == "hist" else {}
+    if kind == "words":
+        # the 32 streams' words of the PREVIOUS clock leave the shared-memory stage while this clock computes:
+        # one drain macro (one stream index j) every 8 steps
+        hooks = {8 * j + 4: ["CLT256V2_W_DRAIN(%d)" % j] for j in range(32)}
     tail, tail_ops = tail_lines(shape, kind) if (shape is not None and kind not in ("words", "plain")) else ([], {})
     per_step = -(-len(tail) // TAIL_STEPS) if tail else 0
     heap = BitHeap(em)
