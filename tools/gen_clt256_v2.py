@@ -85,37 +85,6 @@ def pick_residents(rows, pos, nres, budget):
     return chosen
 
 
-SHARE = int(os.environ.get("CLT256V2_SHARE", "0"))    # 1: fold tap pairs that two rows have in common only once
-
-
-def shared_pairs(rows, pos, resident):
-    """Tap pairs (a, b) that occur in exactly two rows (24 in n256): a ^ b is computed once, when the later of the two
-    planes arrives, and each of the two rows folds it with its other taps -- one LOP3 saved per pair.  Rows take part
-    in at most one pair; a pair is skipped when one of its planes is resident and its new value would be finished
-    before the pair is formed (the register still has to hold the old value then).
-    Returns {row: (a, b)} and {(a, b): [r1, r2]}."""
-    if not SHARE:
-        return {}, {}
-    import itertools
-    occ = {}
-    for r, row in enumerate(rows):
-        for a, b in itertools.combinations(sorted(row), 2):
-            occ.setdefault((a, b), []).append(r)
-    done = [max(pos[t] for t in rows[r]) for r in range(N)]
-    row_pair, pair_rows, used = {}, {}, set()
-    for (a, b), rs in sorted(occ.items()):
-        if len(rs) != 2 or (set(rs) & used):
-            continue
-        tp = max(pos[a], pos[b])
-        if any(x in resident and not tp < done[x] for x in (a, b)):
-            continue
-        pair_rows[(a, b)] = rs
-        for r in rs:
-            row_pair[r] = (a, b)
-        used |= set(rs)
-    return row_pair, pair_rows
-
-
 def slot_map(pos, resident):
     """load time -> compact shared-memory slot, in load order, skipping resident planes"""
     perm = [0] * N
@@ -201,16 +170,10 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
     perm = [0] * N
     for b, p in enumerate(pos):
         perm[p] = b
-    row_pair, pair_rows = shared_pairs(rows, pos, resident)
     taps_at = [[] for _ in range(N)]          # time -> rows tapping the plane loaded then
     for r in range(N):
         for b in rows[r]:
-            if r in row_pair and b in row_pair[r]:
-                continue                      # reaches the row through the shared pair
             taps_at[pos[b]].append(r)
-    pairs_at = {}                             # time -> pairs formed then (both planes have arrived)
-    for (a, b) in pair_rows:
-        pairs_at.setdefault(max(pos[a], pos[b]), []).append((a, b))
     hooks = rmw_hooks_v2() if kind == "hist" else {}
     if kind == "words":
         # the 32 streams' words of the PREVIOUS clock leave the shared-memory stage while this clock computes:
@@ -221,10 +184,9 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
     heap = BitHeap(em)
     pending = {r: [] for r in range(N)}       # raw planes not yet folded
     acc = {}                                  # row -> partial sum expr
-    left = {r: len(rows[r]) - (1 if r in row_pair else 0) for r in range(N)}     # operands still to come (a pair is one)
+    left = {r: len(rows[r]) for r in range(N)}
     store_at = {}                             # time -> [(slot, expr)]
-    old_uses_left = {b: sum(1 for r in range(N) if b in rows[r] and not (r in row_pair and b in row_pair[r]))
-                     + sum(1 for pr in pair_rows if b in pr) for b in resident}
+    old_uses_left = {b: sum(1 for r in range(N) if b in rows[r]) for b in resident}
     assigned = set()
 
     slot_of = slot_map(pos, resident)         # load time -> shared-memory slot (resident planes have none)
@@ -264,9 +226,11 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
         if kind not in ("words", "plain"):
             heap.add(w, parity(perm[t]) == 1)
             heap.reduce()
-        def deliver(r, operand):
-            pending[r].append(operand)
+        for r in taps_at[t]:
+            pending[r].append(w)
             left[r] -= 1
+            if perm[t] in resident:
+                old_uses_left[perm[t]] -= 1
             if r not in acc and len(pending[r]) == 3:
                 nm = em.tmp()
                 em.emit("const uint32_t %s = %s ^ %s ^ %s;" % (nm, *pending[r]))
@@ -283,21 +247,6 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
                 em.emit("const uint32_t %s = %s;" % (nm, " ^ ".join(terms)))
                 em.ops["rec"] += 1
                 finish(r, nm, t)
-
-        # pairs first: they read the OLD values of their planes, which a row finished in this step may overwrite
-        for (a, b) in pairs_at.get(t, []):
-            nm = em.tmp()
-            em.emit("const uint32_t %s = %s ^ %s;" % (nm, wexpr(pos[a]), wexpr(pos[b])))
-            em.ops["rec"] += 1
-            for x in (a, b):
-                if x in resident:
-                    old_uses_left[x] -= 1
-            for r in pair_rows[(a, b)]:
-                deliver(r, nm)
-        for r in taps_at[t]:
-            if perm[t] in resident:
-                old_uses_left[perm[t]] -= 1
-            deliver(r, w)
     assert not store_at, store_at
     assert not tail
     assert assigned == set(resident)
