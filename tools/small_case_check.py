@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""Small invocations of the kernels written or rewritten in round 2, for compute-sanitizer (memcheck / racecheck):
+"""Small invocations of the kernels written or rewritten in round 2, at small sizes (compute-sanitizer is closed on this pool, so this is the small-case check against the oracle):
 hunt_front_pow_kernel + the sync-free back end, hunt_front_warp_kernel, clt256_words2_kernel (pipelined drain),
 the shaper kernels, the chunked host-buffer delivery.  Results are compared with the oracle as usual."""
 import os
