@@ -5,6 +5,7 @@ raises.  `build()` (also called by __graft_entry__.build) compiles the library i
 for sm_100a.
 """
 import ctypes as C
+import functools
 import os
 import subprocess
 
@@ -423,14 +424,20 @@ class Context:
         return res
 
 
-def prbs_spec_state(k, first_bit, m=0, seed=1):
-    """State of a locked detector just before bit `first_bit` (bbb_prbs_spec_state; host arithmetic,
-    needs no GPU)."""
+@functools.lru_cache(maxsize=1024)
+def _prbs_spec_state_tuple(k, first_bit, m, seed):
     det = DetState()
     rc = load().bbb_prbs_spec_state(None, k, first_bit, m, seed, C.byref(det))
     if rc != 0:
         raise BBBError(rc, "bbb_prbs_spec_state(k=%d, first_bit=%d, m=%d)" % (k, first_bit, m))
-    return det
+    return (int(det.bit_in), int(det.prbs), int(det.err_sr), int(det.reload_ctr))
+
+
+def prbs_spec_state(k, first_bit, m=0, seed=1):
+    """State of a locked detector just before bit `first_bit` (bbb_prbs_spec_state; host arithmetic,
+    needs no GPU).  Memoised: a sharded loop asks for the same boundary every step, and the call rebuilds the
+    k x k jump tables."""
+    return DetState(*_prbs_spec_state_tuple(int(k), int(first_bit), int(m), int(seed)))
 
 
 def clt_value(n, x, model=MODEL_GATEWARE):

@@ -7,11 +7,11 @@ tests):
   CLT-GRNG fused      rank r owns sample indices [first + r*per, ...) -> all-reduce(sum) of
                       u64[n+3] = histogram | sum g | sum g^2
   PRBS detect         rank r owns a contiguous bit range and starts from the locked detector state
-                      (bbb_prbs_spec_state); end states are all-gathered and a rank whose left
-                      neighbour ended in a different state re-runs its range from that state, until
-                      every rank started where its neighbour ended -> all-reduce(sum) of 5 counters
-  rnghunt sweep       rank r owns candidates first + r, first + r + world, ... -> all-gather of the
-                      k smallest accepted indices, merged; all-reduce(sum) of the stage counts
+                      (bbb_prbs_spec_state); (start, end, counters) are all-gathered and a rank whose
+                      left neighbour ended in a different state re-runs its range from that state, until
+                      every rank started where its neighbour ended; the gathered counters are summed
+  rnghunt sweep       rank r owns candidates first + r, first + r + world, ... -> one all-gather of the
+                      k smallest accepted indices and the 5 stage counts per rank, merged / summed
   materialised streams  disjoint index ranges, each rank writes its own HBM; nothing is exchanged
 
 `engine` is a basebandboard_b200.lib.Context (the CUDA library).  The functions only use its
@@ -82,6 +82,9 @@ def clt_hist_sharded(engine, init, first, count, model=0):
     return acc[:-2].copy(), int(acc[-2:-1].view(np.int64)[0]), int(acc[-1])
 
 
+_KEYS = ("err", "err_valid", "reload_events", "reload_cycles", "injected")
+
+
 def _det_tuple(det):
     return (int(det.bit_in), int(det.prbs), int(det.err_sr), int(det.reload_ctr))
 
@@ -113,17 +116,18 @@ def prbs_detect_sharded(engine, k, nbits, m=0, seed=1, first_bit=0, make_det=Non
             runs += 1
             end = _det_tuple(det) if cnt else start
             ran_from = start
-        table = _all_gather_i64(list(start) + list(end))     # [world, 8]
+        # one exchange per round: (start, end, counters) of every rank; when the chain is consistent the counters of
+        # that same table are the result, so no separate reduction follows
+        table = _all_gather_i64(list(start) + list(end) + [ctr[key] for key in _KEYS])     # [world, 13]
         # the state each rank should have started from: its left neighbour's end state
-        wrong = [r for r in range(1, world) if tuple(table[r][:4]) != tuple(table[r - 1][4:])]
+        wrong = [r for r in range(1, world) if tuple(table[r][:4]) != tuple(table[r - 1][4:8])]
         if not wrong:
             break
         if rank in wrong:
-            start = tuple(int(v) for v in table[rank - 1][4:])
-    keys = ("err", "err_valid", "reload_events", "reload_cycles", "injected")
-    tot = _all_reduce_sum_u64(np.array([ctr[key] for key in keys], dtype=np.uint64))
-    final = tuple(int(v) for v in table[world - 1][4:])
-    return dict(zip(keys, (int(v) for v in tot))), final, runs
+            start = tuple(int(v) for v in table[rank - 1][4:8])
+    tot = table[:, 8:].astype(np.uint64).sum(axis=0, dtype=np.uint64)
+    final = tuple(int(v) for v in table[world - 1][4:8])
+    return dict(zip(_KEYS, (int(v) for v in tot))), final, runs
 
 
 def _loop_sharded(run, spec_state, k, nbits, first_bit, warm_bits=1024):
@@ -151,16 +155,15 @@ def _loop_sharded(run, spec_state, k, nbits, first_bit, warm_bits=1024):
             ctr, end = run(lo, cnt, start) if cnt else (zero, start)
             runs += 1
             ran_from = start
-        table = _all_gather_i64(list(start) + list(end))     # [world, 8]
-        wrong = [r for r in range(1, world) if tuple(table[r][:4]) != tuple(table[r - 1][4:])]
+        table = _all_gather_i64(list(start) + list(end) + [ctr[key] for key in _KEYS])     # [world, 13]
+        wrong = [r for r in range(1, world) if tuple(table[r][:4]) != tuple(table[r - 1][4:8])]
         if not wrong:
             break
         if rank in wrong:
-            start = tuple(int(v) for v in table[rank - 1][4:])
-    keys = ("err", "err_valid", "reload_events", "reload_cycles", "injected")
-    tot = _all_reduce_sum_u64(np.array([ctr[key] for key in keys], dtype=np.uint64))
-    final = tuple(int(v) for v in table[world - 1][4:])
-    return dict(zip(keys, (int(v) for v in tot))), final, runs
+            start = tuple(int(v) for v in table[rank - 1][4:8])
+    tot = table[:, 8:].astype(np.uint64).sum(axis=0, dtype=np.uint64)
+    final = tuple(int(v) for v in table[world - 1][4:8])
+    return dict(zip(_KEYS, (int(v) for v in tot))), final, runs
 
 
 def prbs_slicer_detect_sharded(engine, k, nbits, init=1, amplitude=256, noise_var=8, spb=8, delay=0, first_bit=0,
@@ -202,12 +205,13 @@ def rnghunt_sweep_sharded(engine, n, seed, first, count, k=16):
     res = engine.rnghunt_sweep(n, seed, first + rank, mine, k=k, stride=world) if mine else \
         {"best": [], "stage_counts": np.zeros(5, dtype=np.uint64)}
     best = list(res["best"])[:k]
-    pad = np.full(k + 1, -1, dtype=np.int64)
+    pad = np.full(k + 1 + 5, -1, dtype=np.int64)       # one exchange: count | k indices | 5 stage counts
     pad[0] = len(best)
     pad[1:1 + len(best)] = best
+    pad[k + 1:] = np.asarray(res["stage_counts"], dtype=np.uint64).view(np.int64)
     allb = _all_gather_i64(pad)
     merged = sorted(int(v) for row in allb for v in row[1:1 + int(row[0])])[:k]
-    counts = _all_reduce_sum_u64(np.asarray(res["stage_counts"], dtype=np.uint64))
+    counts = allb[:, k + 1:].astype(np.uint64).sum(axis=0, dtype=np.uint64)
     return {"best": merged, "stage_counts": counts}
 
 

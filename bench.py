@@ -261,7 +261,7 @@ def run_rnghunt_leg(args, ctx, rank, world, local_rank, lop3_peak, barrier):
         "scaling": "strong", "dtype": "u32 GF(2)",
         "config": {"workload": "rnghunt sweep n=%d, seed %d, fixed candidate set [0, 2^%d) interleaved c = rank (mod N), "
                                "merged best-%d (BASELINE.json configs[3])" % (HUNT_N, HUNT_SEED, args.hunt_log2, HUNT_K),
-                   "collective": "all-gather of k indices + all-reduce of 5 stage counts, inside the timed region"
+                   "collective": "one all-gather of k indices + 5 stage counts per rank, inside the timed region"
                                  if world > 1 else "none"},
         "wall_ms_per_step": wall_ms / args.steps, "clocks": clocks,
         "e2e": {"value": total / (e2e_ms * 1e-3), "unit": "candidates/s", "h2d_bytes_per_step": h2d,
