@@ -1320,16 +1320,11 @@ static int hunt_sweep(bbb_ctx *c, uint32_t n, uint64_t seed, uint64_t first, uin
     BBB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
     std::vector<HuntHit> found;
     uint32_t turn = 0;
-    // the back end of the LAST batch has no front kernel to hide behind: end the call with two short batches
-    const uint64_t tail_each = (!c->tune_hunt_batch && count >= (1u << 19)) ? (1u << 16) : 0;
-    uint32_t nb = 0;
-    for (uint64_t done = 0; done < count; done += nb, turn ^= 1u) {
+    for (uint64_t done = 0; done < count; done += cap, turn ^= 1u) {
         HuntSlot &b = slots[turn];
         rc = hunt_collect(c, b, stride, nwp, found);          // the batch that used this slot two turns ago
         if (rc) return rc;
-        const uint64_t left = count - done;
-        nb = (uint32_t)(left <= 2 * tail_each ? (left > tail_each ? tail_each : left)
-                                              : (left - 2 * tail_each < cap ? left - 2 * tail_each : cap));
+        const uint32_t nb = (uint32_t)(count - done < cap ? count - done : cap);
         BBB_CUDA(c, cudaMemsetAsync(b.counters, 0, 16, b.stream));
         FrontParams p;
         p.n = n; p.seed = seed; p.first = first + done * stride; p.stride = stride; p.count = nb;
