@@ -272,12 +272,16 @@ def run_rnghunt_leg(args, ctx, rank, world, local_rank, lop3_peak, barrier):
                      "launch_ms_per_2p20": sweep_ms / max(1.0, total / world / (1 << 20)),
                      "kernel": "hunt_front_pow<6,8>",
                      "alu_pipe_busy_ncu": 0.83,
+                     "survey_tap_xors_per_candidate": int(2 * HUNT_N * HUNT_N * 31 / 8),
+                     "survey_tap_xor_rate_T_per_s": per_gpu * (2 * HUNT_N * HUNT_N * 31 / 8) / 1e12,
                      "note": "algorithmic work = (2n/8) passes of A^8 over 7 row groups x (6 mask LOP3 + 1 parity predicate) "
                              "+ 7 sparse products A.P (4 taps x 6 word-XORs per row) = %d thread-instr per candidate "
                              "(binary_matrix.rs:68-76); candidate generation (binary_matrix.rs:81-101), Berlekamp-Massey, "
                              "votes and the primitivity stage are NOT counted, which is why frac is far below the ALU-pipe "
                              "utilisation ncu reports for the kernel (83 %%, profiles/r2_rnghunt_pow8_ncu_full.txt); peak = "
-                             "LOP3 issue rate measured live (bbb_measure_lop3_peak); HBM traffic ~0" % alg},
+                             "LOP3 issue rate measured live (bbb_measure_lop3_peak); HBM traffic ~0.  For continuity with "
+                             "round 1 (one operation per tap of SURVEY 8d's 2n x 31n/8 tap-XORs): survey_tap_xor_rate_T_per_s, "
+                             "which A^K lets exceed one-instruction-per-tap formulations" % alg},
         "result_check": {"best": [int(b) for b in res["r"]["best"]],
                          "stage_counts": [int(v) for v in res["r"]["stage_counts"]]},
     }
