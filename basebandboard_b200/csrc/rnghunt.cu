@@ -1038,7 +1038,7 @@ static int hunt_setup(bbb_ctx *c, uint32_t n, uint32_t cap, uint32_t nwp, bool w
         for (uint32_t w = BBB_MF_ENTRIES[e0 + i]; w < BBB_MF_ENTRIES[e0 + i + 1]; w++) words.push_back(BBB_MF_WORDS[w]);
     }
     off[sh.nf] = (uint32_t)words.size();
-    const uint32_t hit_cap = cap;                  // every candidate of a batch may be a hit (small n: 1 in 10)
+    const uint32_t hit_cap = cap;                  // sized for the worst case: every candidate of a batch accepted
     size_t at = 0, hat = 0;
     auto take = [&](size_t bytes) { size_t o = at; at += align256(bytes); return o; };
     auto htake = [&](size_t bytes) { size_t o = hat; hat += align256(bytes); return o; };

@@ -62,6 +62,19 @@ def test_sweep_stages_match_oracle(ctx, orc, n, count):
         assert len(hits) > 0 and counts[STAGE_ORDER] > 0 and counts[STAGE_FILTER] > 0
 
 
+def test_sweep_small_n_many_hits(ctx, orc):
+    """n = 8: almost 1 % of the candidates are accepted, so a batch returns more than a thousand hits (and their
+    polynomials) through the pinned hit list."""
+    n, seed, count = 8, 4, 150000
+    stages, counts = orc.rnghunt_sweep(n, seed, 0, count, threads=os.cpu_count() or 1)
+    hits = [int(i) for i in np.nonzero(stages == STAGE_PRIMITIVE)[0]]
+    assert len(hits) > 1000
+    got = ctx.rnghunt_sweep(n, seed, 0, count, k=count)
+    assert got["best"] == hits and np.array_equal(got["stage_counts"], counts)
+    gp = ctx.rnghunt_sweep(n, seed, 0, count, k=count, want_polys=True)
+    assert gp["best"] == hits and all(w % 2 == 1 and 3 <= w <= 9 for w in gp["weights"])
+
+
 def test_sweep_stride_offset_and_batches(ctx, orc):
     """Interleaved candidate indices (the multi-GPU partition) and small device batches."""
     n, seed = 32, 5
