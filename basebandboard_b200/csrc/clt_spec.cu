@@ -591,16 +591,28 @@ clt256_words_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
 #define CLT256V2W_SMEM (CLT256V2_STATE_BYTES + CLT256V2W_STAGE_WORDS * 4)
 
 // stage word (stream j, word w) of thread `tid` lives in column tid ^ 16*(w >> 2): the two lanes that later
-// fetch the two halves of one thread's 32-byte piece then hit different banks
+// fetch the two halves of one thread's 32-byte piece then hit different banks.
+// The eight emits of a clock run as ONE loop: a switch copies the 32 source planes of word w into tw[], the
+// transpose and the staging stores exist once.  (Straight-line, the loop body of this kernel was ~5500 instructions
+// = 88 KB: ncu showed 0.57 no-instruction stalls per issued instruction, four warps streaming different parts of it.)
+#define CLT256V2_W_BEGIN                                                                                             \
+    __syncwarp();                        /* every lane has drained the previous clock's words */                     \
+    _Pragma("unroll 1") for (uint32_t w_ = 0; w_ < 8u; w_++) {                                                       \
+        uint32_t tw[32];                                                                                             \
+        switch (w_) {
 #define CLT256V2_W_EMIT(w, r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18, r19, \
                         r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31)                                  \
-    {                                                                                                                \
-        uint32_t tw[32] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18,       \
-                           r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31};                          \
+        case w: {                                                                                                    \
+            const uint32_t src[32] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16,     \
+                                      r17, r18, r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31};    \
+            _Pragma("unroll") for (int i = 0; i < 32; i++) tw[i] = src[i];                                           \
+        } break;
+#define CLT256V2_W_END                                                                                               \
+        }                                                                                                            \
         transpose32_fast(tw);                                                                                        \
-        if ((w) == 0) __syncwarp();      /* every lane has drained the previous clock's words */                       \
+        const uint32_t sa = (w_ < 4u ? stage_a : stage_b) + w_ * (uint32_t)(CLT256V2_B * 4);                         \
         _Pragma("unroll") for (int j = 0; j < 32; j++)                                                               \
-            asm volatile("st.shared.u32 [%0], %1;" ::"r"(((w) < 4 ? stage_a : stage_b) + (uint32_t)((j * 8 + (w)) * CLT256V2_B * 4)), "r"(tw[j])); \
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(sa + (uint32_t)(j * 8 * CLT256V2_B * 4)), "r"(tw[j]));      \
     }
 
 // One stream index j of the PREVIOUS clock leaves the stage (the generator places 32 of these between the steps of
@@ -692,8 +704,14 @@ clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #undef CLT256V2_B
 #undef CLT256V2_W_EMIT
 #pragma push_macro("CLT256V2_W_DRAIN")
+#pragma push_macro("CLT256V2_W_BEGIN")
+#pragma push_macro("CLT256V2_W_END")
 #undef CLT256V2_W_DRAIN
+#undef CLT256V2_W_BEGIN
+#undef CLT256V2_W_END
 #define CLT256V2_W_DRAIN(j)
+#define CLT256V2_W_BEGIN
+#define CLT256V2_W_END
 #define CLT256V2_B 192
 #define CLT256V3W_STAGE_WORDS (32 * 4 * 192)
 #define CLT256V3W_STATE_BYTES (CLT256V2_NSLOTS * 192 * 4)
@@ -739,6 +757,8 @@ clt256_words3_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #undef CLT256V2_SECTION_W_BODY
     }
 }
+#pragma pop_macro("CLT256V2_W_END")
+#pragma pop_macro("CLT256V2_W_BEGIN")
 #pragma pop_macro("CLT256V2_W_DRAIN")
 #pragma pop_macro("CLT256V2_W_EMIT")
 #pragma pop_macro("CLT256V2_B")

@@ -256,11 +256,15 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
     if kind == "words":
         # raw URNG words: the state AFTER the clock, un-sliced 32 planes at a time (resident planes from
         # their registers, the others from their slots, where the clock has just stored them)
+        # BEGIN / END let a kernel wrap the eight emits in ONE loop (a switch picks the 32 source planes of word wd,
+        # the transpose and the staging code exist once): the straight-line version was 8 x 300 instructions
+        em.emit("CLT256V2_W_BEGIN")
         for wd in range(N // 32):
             src = []
             for b in range(32 * wd, 32 * wd + 32):
                 src.append(("r%d" % b) if b in resident else "st[%d * CLT256V2_B]" % slot_of[pos[b]])
             em.emit("CLT256V2_W_EMIT(%d, %s)" % (wd, ", ".join(src)))
+        em.emit("CLT256V2_W_END")
         return em, perm
     new_shape = [[neg for _, neg in heap.heap[w]] for w in range(10)]
     if shape is None:
