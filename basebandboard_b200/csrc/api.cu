@@ -315,6 +315,7 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
     else if (!strcmp(key, "clt_spec_variant")) c->tune_spec_variant = value == 1 ? 1 : 2;
     else if (!strcmp(key, "clt_spec_min_steps")) c->tune_spec_min_steps = value < 1 ? 1u : (uint32_t)value;
     else if (!strcmp(key, "clt_spec_max_blocks")) c->tune_spec_max_blocks = value < 0 ? 0u : (uint32_t)value;
+    else if (!strcmp(key, "words_variant")) c->tune_words_variant = (int)value;
     else if (!strcmp(key, "words_b192")) c->tune_words_b192 = value != 0;
     else if (!strcmp(key, "dec_full_stream")) c->tune_dec_full_stream = value != 0;
     else if (!strcmp(key, "slicer_chunk_bits")) c->tune_slicer_chunk_bits = value < 64 ? 0ull : ((uint64_t)value & ~63ull);

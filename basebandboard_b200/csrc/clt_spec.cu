@@ -232,7 +232,8 @@ clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
 // CTAs of the fused kernel one SM holds at a time
 int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c, int kind)
 {
-    return c->tune_spec_variant == 1 || kind == 2 ? 1 : CLT256V2_CTAS_PER_SM;
+    if (kind == 2) return (c->tune_spec_variant != 1 && c->tune_words_variant == 4) ? 2 : 1;
+    return c->tune_spec_variant == 1 ? 1 : CLT256V2_CTAS_PER_SM;
 }
 
 // Streams one CTA carries, and whether the loaded recurrence has a specialised kernel.
@@ -691,6 +692,124 @@ clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 }
 
 // ---------------------------------------------------------------------------
+// clt256_words4_kernel: the raw-word stream with TWO CTAs per SM.  words2 keeps a whole clock of un-sliced words
+// (32 streams x 8 words x 128 threads = 128 KB) in shared memory, so only four warps fit an SM and each scheduler has
+// one warp whose dependency and shared-memory latencies nobody hides (ncu: issue slots 31 % used, ALU 37 %).  Here a
+// clock is un-sliced in four groups of 8 streams: for group g and word w the kernel takes byte g of the 32 planes of
+// the word (24 PRMT pack them into 8 words, byte b of word k = plane 8b+k) and transposes the 8x8 bit matrices
+// (3 stages x 4 pairs), which yields word w of the 8 streams directly -- 72 ALU instructions where a full 32x32
+// transpose costs 256 for 32 streams, so the total is the same.  The stage holds 8 streams x 8 words (32 KB), lane
+// pairs then store complete 32-byte sectors as in words2, and state + stage = 108 KB: two CTAs, eight warps per SM.
+// ---------------------------------------------------------------------------
+#pragma push_macro("CLT256V2_W_DRAIN")
+#pragma push_macro("CLT256V2_W_BEGIN")
+#pragma push_macro("CLT256V2_W_EMIT")
+#pragma push_macro("CLT256V2_W_END")
+#undef CLT256V2_W_DRAIN
+#undef CLT256V2_W_BEGIN
+#undef CLT256V2_W_EMIT
+#undef CLT256V2_W_END
+#define CLT256V4W_STAGE_BYTES (8 * 8 * CLT256V2_B * 4)
+#define CLT256V4W_SMEM (CLT256V2_STATE_BYTES + CLT256V4W_STAGE_BYTES)
+
+__device__ __forceinline__ uint32_t prmt_r(uint32_t a, uint32_t b, uint32_t sel)
+{
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+
+// tw[i] = plane i of a word (bit j = stream j).  Returns in o[s] the word of stream 8g+s: bit i = bit 8g+s of tw[i].
+__device__ __forceinline__ void unslice8(const uint32_t (&tw)[32], uint32_t sel2, uint32_t (&o)[8])
+{
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const uint32_t lo = prmt_r(tw[k], tw[8 + k], sel2), hi = prmt_r(tw[16 + k], tw[24 + k], sel2);
+        o[k] = __byte_perm(lo, hi, 0x5410);          // byte b = byte g of plane 8b + k
+    }
+#pragma unroll
+    for (int st = 0; st < 3; st++) {
+        const int j = 4 >> st;
+        const uint32_t m = st == 0 ? 0x0F0F0F0Fu : st == 1 ? 0x33333333u : 0x55555555u;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if (k & j) continue;
+            const uint32_t x = o[k], y = o[k + j];
+            o[k] = (x & m) | ((y << j) & ~m);
+            o[k + j] = ((x >> j) & m) | (y & ~m);
+        }
+    }
+}
+
+#define CLT256V2_W_DRAIN(j)
+#define CLT256V2_W_BEGIN                                                                                             \
+    _Pragma("unroll 1") for (uint32_t g_ = 0; g_ < 4u; g_++) {                                                       \
+        const uint32_t sel2 = g_ | ((4u + g_) << 4);                                                                 \
+        _Pragma("unroll 1") for (uint32_t w_ = 0; w_ < 8u; w_++) {                                                   \
+            uint32_t tw[32];                                                                                         \
+            switch (w_) {
+#define CLT256V2_W_EMIT(w, r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18, r19, \
+                        r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31)                                  \
+            case w: {                                                                                                \
+                const uint32_t src[32] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, \
+                                          r17, r18, r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31}; \
+                _Pragma("unroll") for (int i = 0; i < 32; i++) tw[i] = src[i];                                       \
+            } break;
+#define CLT256V2_W_END                                                                                               \
+            }                                                                                                        \
+            uint32_t o[8];                                                                                           \
+            unslice8(tw, sel2, o);                                                                                   \
+            const uint32_t sa = (w_ < 4u ? stage_a : stage_b) + w_ * (uint32_t)(CLT256V2_B * 4);                     \
+            _Pragma("unroll") for (int s8 = 0; s8 < 8; s8++)                                                         \
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(sa + (uint32_t)(s8 * 8 * CLT256V2_B * 4)), "r"(o[s8])); \
+        }                                                                                                            \
+        __syncwarp();                                                                                                \
+        _Pragma("unroll") for (int s8 = 0; s8 < 8; s8++) {                                                           \
+            uint32_t v[8];                                                                                           \
+            _Pragma("unroll") for (int i = 0; i < 4; i++) {                                                          \
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[i]) : "r"(rd0 + (uint32_t)((s8 * 8 + i) * CLT256V2_B * 4)));     \
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[4 + i]) : "r"(rd1 + (uint32_t)((s8 * 8 + i) * CLT256V2_B * 4))); \
+            }                                                                                                        \
+            const size_t off = ((size_t)(g_ * 8u + s8) * L + it) * 8u;                                               \
+            CLT256V2W_STORE((uint4 *)(op0 + off), make_uint4(v[0], v[1], v[2], v[3]));                               \
+            CLT256V2W_STORE((uint4 *)(op1 + off), make_uint4(v[4], v[5], v[6], v[7]));                               \
+        }                                                                                                            \
+        __syncwarp();                                                                                                \
+    }
+
+__global__ void __launch_bounds__(CLT256V2_B, 2)
+clt256_words4_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+    uint32_t *const st = (uint32_t *)smem4 + tid;
+    for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+    const uint32_t stage_base = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
+    const uint32_t stage_a = stage_base + tid * 4u, stage_b = stage_base + (tid ^ 16u) * 4u;
+    const uint32_t lane = tid & 31u, q = lane >> 1, h = lane & 1u, wbase = tid & ~31u;
+    const uint32_t u0 = wbase + q, u1 = u0 + 16u;
+    const uint32_t rd0 = stage_base + ((4u * h) * CLT256V2_B + (u0 ^ (16u * h))) * 4u;
+    const uint32_t rd1 = stage_base + ((4u * h) * CLT256V2_B + (u1 ^ (16u * h))) * 4u;
+    uint32_t *const op0 = out + (size_t)(blockIdx.x * CLT256V2_B + u0) * 32u * L * 8u + 4u * h;   // stream j, clock it: + (j*L + it)*8
+    uint32_t *const op1 = out + (size_t)(blockIdx.x * CLT256V2_B + u1) * 32u * L * 8u + 4u * h;
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_W_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_W_BODY
+    }
+}
+#pragma pop_macro("CLT256V2_W_END")
+#pragma pop_macro("CLT256V2_W_EMIT")
+#pragma pop_macro("CLT256V2_W_BEGIN")
+#pragma pop_macro("CLT256V2_W_DRAIN")
+
+// ---------------------------------------------------------------------------
 // clt256_words3_kernel (EXPERIMENT, knob "words_b192"; measured and rejected): the same clock and transposes with
 // SIX warps per SM instead of four.  ncu on words2 shows neither pipe busy (ALU 34 %, LSU 36 %), so more warps
 // looked like the fix; but 192 threads need 114 KB of state, which leaves room for only HALF a clock of staging
@@ -793,6 +912,11 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
                                                                              (int32_t)noise_var);
         c->last_kernel = "clt256_s16";
+    } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 4) {
+        static_assert(2 * (CLT256V4W_SMEM + 1024) <= 228 * 1024, "shared memory budget");
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_words4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V4W_SMEM));
+        clt256_words4_kernel<<<blocks, CLT256V2_B, CLT256V4W_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
+        c->last_kernel = "clt256_words4";
     } else if (c->tune_spec_variant != 1 && c->tune_words_b192) {
         static_assert(CLT256V3W_SMEM <= 227 * 1024, "shared memory budget");
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V3W_SMEM));
