@@ -4,6 +4,7 @@ import torch
 from basebandboard_b200 import lib
 ctx = lib.Context(0)
 ctx.lutopt_load_shipped(256)
+ctx.set_tuning("words_variant", int(os.environ.get("WORDS_VARIANT", "0")))
 n = 1 << 27
 buf = torch.empty(n * 4, dtype=torch.int64, device="cuda")
 for _ in range(2):
