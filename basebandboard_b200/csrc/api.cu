@@ -186,17 +186,25 @@ int bbb_stream_to_host(bbb_ctx *c, int dev_slot, void *out, size_t total, size_t
         threads = std::thread::hardware_concurrency();
         threads = threads > 8 ? 8 : (threads ? threads : 1);
     }
+    // a caller that hands in page-locked memory (cudaHostAlloc / cudaHostRegister, e.g. a pinned torch tensor) gets the
+    // chunks copied straight into it: no staging buffer, no host-side copy
+    bool direct = false;
+    {
+        cudaPointerAttributes attr;
+        if (total && cudaPointerGetAttributes(&attr, out) == cudaSuccess) direct = attr.type == cudaMemoryTypeHost;
+        cudaGetLastError();                          // an unregistered pointer is not an error here
+    }
     c->begin_call();
     struct Nest { bbb_ctx *c; Nest(bbb_ctx *cc) : c(cc) { c->nest++; } ~Nest() { c->nest--; } } nest(c);
     char *d = (char *)c->scratch(dev_slot, 2 * slot_bytes);
-    char *h = (char *)c->pinned(1, 2 * slot_bytes);
+    char *h = direct ? (char *)out : (char *)c->pinned(1, 2 * slot_bytes);
     if (!d || !h) return BBB_ECUDA;
     const size_t nchunks = (total + chunk - 1) / chunk;
     auto drain = [&](size_t i) -> int {
         const int slot = (int)(i & 1);
         const size_t off = i * chunk, bytes = total - off < chunk ? total - off : chunk;
-        BBB_CUDA(c, cudaEventSynchronize(c->ev_slot[slot]));
-        host_copy_parallel((char *)out + off, h + slot * slot_bytes, bytes, threads);
+        BBB_CUDA(c, cudaEventSynchronize(c->ev_slot[slot]));      // (direct: the device buffer is free again)
+        if (!direct) host_copy_parallel((char *)out + off, h + slot * slot_bytes, bytes, threads);
         return BBB_OK;
     };
     for (size_t i = 0; i < nchunks; i++) {
@@ -206,7 +214,8 @@ int bbb_stream_to_host(bbb_ctx *c, int dev_slot, void *out, size_t total, size_t
         if (rc) return rc;
         BBB_CUDA(c, cudaEventRecord(c->ev_aux[slot], c->stream));
         BBB_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_aux[slot], 0));
-        BBB_CUDA(c, cudaMemcpyAsync(h + slot * slot_bytes, d + slot * slot_bytes, bytes, cudaMemcpyDeviceToHost, c->stream2));
+        BBB_CUDA(c, cudaMemcpyAsync(direct ? h + off : h + slot * slot_bytes, d + slot * slot_bytes, bytes,
+                                    cudaMemcpyDeviceToHost, c->stream2));
         c->d2h_bytes += bytes;
         BBB_CUDA(c, cudaEventRecord(c->ev_slot[slot], c->stream2));
         if (i) { rc = drain(i - 1); if (rc) return rc; }             // chunk i-1 leaves the staging buffer meanwhile

@@ -67,6 +67,23 @@ def test_stream_unaligned_device_pointer(ctx, orc):
     assert int(buf[0]) == 0
 
 
+def test_stream_into_pinned_and_pageable_host_buffers(ctx, orc):
+    """bbb_prbs_stream delivers the same words into a page-locked caller buffer (chunks copied straight into it) and
+    into a pageable one (pinned staging + host copy); several chunks, ragged last chunk."""
+    import torch
+    nbits = 64 * (3 * 8192 + 777)
+    want, _ = orc.prbs_bits(23, nbits)
+    ctx.set_tuning("stream_chunk_bytes", 1 << 16)
+    try:
+        pinned = torch.empty(nbits // 8, dtype=torch.uint8, pin_memory=True).numpy().view(np.uint64)
+        pinned[:] = 0
+        got_p = ctx.prbs_stream(23, nbits, out=pinned)
+        got_h = ctx.prbs_stream(23, nbits, out=np.ones(nbits // 64, dtype=np.uint64))
+    finally:
+        ctx.set_tuning("stream_chunk_bytes", 0)
+    assert np.array_equal(got_p, want) and np.array_equal(got_h, want)
+
+
 def test_stream_large_window_properties(ctx):
     """2^33 bits (1 GiB) of PRBS-31 on the device: every word obeys W[j] = W[j-31] ^ W[j-28]
     and the stream continues exactly where a second call starts."""
