@@ -232,7 +232,7 @@ clt256_hist2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L,
 // CTAs of the fused kernel one SM holds at a time
 int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c, int kind)
 {
-    if (kind == 2) return (c->tune_spec_variant != 1 && c->tune_words_variant == 4) ? 2 : 1;
+    if (kind == 2) return (c->tune_spec_variant != 1 && (c->tune_words_variant == 4 || c->tune_words_variant == 5)) ? 2 : 1;
     return c->tune_spec_variant == 1 ? 1 : CLT256V2_CTAS_PER_SM;
 }
 
@@ -810,6 +810,89 @@ clt256_words4_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #pragma pop_macro("CLT256V2_W_DRAIN")
 
 // ---------------------------------------------------------------------------
+// clt256_words5_kernel (knob words_variant = 5): words2 with the un-sliced clock staged in an L2-resident global
+// slab [word][stream][thread] (coalesced 128-byte rows in both directions: 1 KB per thread, 39 MB for the grid)
+// instead of 128 KB of shared memory, which leaves room for two CTAs = eight warps per SM.  The lane pairs read
+// their halves back with L1-bypassing loads and store complete sectors exactly as in words2.
+// ---------------------------------------------------------------------------
+#pragma push_macro("CLT256V2_W_DRAIN")
+#pragma push_macro("CLT256V2_W_BEGIN")
+#pragma push_macro("CLT256V2_W_EMIT")
+#pragma push_macro("CLT256V2_W_END")
+#undef CLT256V2_W_DRAIN
+#undef CLT256V2_W_BEGIN
+#undef CLT256V2_W_EMIT
+#undef CLT256V2_W_END
+#define CLT256V2_W_DRAIN(j)                                                                                          \
+    if (it != 0u) {                                                                                                  \
+        uint32_t v[8];                                                                                               \
+        _Pragma("unroll") for (int i = 0; i < 4; i++) {                                                              \
+            v[i] = __ldcg(rd0 + (size_t)((4u * h + i) * 32u + (j)) * T);                                             \
+            v[4 + i] = __ldcg(rd1 + (size_t)((4u * h + i) * 32u + (j)) * T);                                         \
+        }                                                                                                            \
+        const size_t off = ((size_t)(j) * L + (it - 1u)) * 8u;                                                       \
+        CLT256V2W_STORE((uint4 *)(op0 + off), make_uint4(v[0], v[1], v[2], v[3]));                                   \
+        CLT256V2W_STORE((uint4 *)(op1 + off), make_uint4(v[4], v[5], v[6], v[7]));                                   \
+    }
+#define CLT256V2_W_BEGIN                                                                                             \
+    __syncwarp();                        /* every lane has drained the previous clock's words */                     \
+    _Pragma("unroll 1") for (uint32_t w_ = 0; w_ < 8u; w_++) {                                                       \
+        uint32_t tw[32];                                                                                             \
+        switch (w_) {
+#define CLT256V2_W_EMIT(w, r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18, r19, \
+                        r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31)                                  \
+        case w: {                                                                                                    \
+            const uint32_t src[32] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16,     \
+                                      r17, r18, r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31};    \
+            _Pragma("unroll") for (int i = 0; i < 32; i++) tw[i] = src[i];                                           \
+        } break;
+#define CLT256V2_W_END                                                                                               \
+        }                                                                                                            \
+        transpose32_fast(tw);                                                                                        \
+        uint32_t *const sw = slab_w + (size_t)w_ * 32u * T;                                                          \
+        _Pragma("unroll") for (int j = 0; j < 32; j++) __stcg(sw + (size_t)j * T, tw[j]);                            \
+    }
+
+__global__ void __launch_bounds__(CLT256V2_B, 2)
+clt256_words5_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out,
+                     uint32_t *__restrict__ slab)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+    uint32_t *const st = (uint32_t *)smem4 + tid;
+    for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+    const uint32_t lane = tid & 31u, q = lane >> 1, h = lane & 1u, wbase = tid & ~31u;
+    const uint32_t u0 = wbase + q, u1 = u0 + 16u;
+    uint32_t *const slab_w = slab + t;                                        // this thread's column of the slab
+    const uint32_t *const rd0 = slab + blockIdx.x * CLT256V2_B + u0;          // the columns this lane stores for
+    const uint32_t *const rd1 = slab + blockIdx.x * CLT256V2_B + u1;
+    uint32_t *const op0 = out + (size_t)(blockIdx.x * CLT256V2_B + u0) * 32u * L * 8u + 4u * h;   // stream j, clock it: + (j*L + it)*8
+    uint32_t *const op1 = out + (size_t)(blockIdx.x * CLT256V2_B + u1) * 32u * L * 8u + 4u * h;
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < L; it++) {
+        __syncwarp();                    // the slab holds clock it-1 of every lane's threads
+#define CLT256V2_SECTION_W_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_W_BODY
+    }
+    __syncwarp();
+    {
+        const uint32_t it = L;
+#pragma unroll 4
+        for (int j = 0; j < 32; j++) { CLT256V2_W_DRAIN(j) }
+    }
+}
+#pragma pop_macro("CLT256V2_W_END")
+#pragma pop_macro("CLT256V2_W_EMIT")
+#pragma pop_macro("CLT256V2_W_BEGIN")
+#pragma pop_macro("CLT256V2_W_DRAIN")
+
+// ---------------------------------------------------------------------------
 // clt256_words3_kernel (EXPERIMENT, knob "words_b192"; measured and rejected): the same clock and transposes with
 // SIX warps per SM instead of four.  ncu on words2 shows neither pipe busy (ALU 34 %, LSU 36 %), so more warps
 // looked like the fix; but 192 threads need 114 KB of state, which leaves room for only HALF a clock of staging
@@ -912,6 +995,13 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
                                                                              (int32_t)noise_var);
         c->last_kernel = "clt256_s16";
+    } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 5) {
+        const uint32_t T = blocks * CLT256V2_B;
+        uint32_t *slab = (uint32_t *)c->scratch(11, (size_t)256 * T * 4);
+        if (!slab) return BBB_ECUDA;
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_words5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2_STATE_BYTES));
+        clt256_words5_kernel<<<blocks, CLT256V2_B, CLT256V2_STATE_BYTES, c->stream>>>(planes, T, L, (uint32_t *)out, slab);
+        c->last_kernel = "clt256_words5";
     } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 4) {
         static_assert(2 * (CLT256V4W_SMEM + 1024) <= 228 * 1024, "shared memory budget");
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V4W_SMEM));

@@ -43,8 +43,8 @@ def main():
     if "streams" in what:
         c.lutopt_load_shipped(256)
         for name, count, bytes_per in (("clt_stream_i8", 1 << 33, 1), ("clt_stream_i16", 1 << 32, 2),
-                                       ("lutopt_stream", 1 << 28, 32), ("lutopt_stream_v4", 1 << 28, 32)):
-            c.set_tuning("words_variant", 4 if name.endswith("v4") else 0)
+                                       ("lutopt_stream", 1 << 28, 32), ("lutopt_stream_v5", 1 << 28, 32)):
+            c.set_tuning("words_variant", 5 if name.endswith("v5") else 0)
             buf = torch.empty(count * bytes_per, dtype=torch.uint8, device="cuda")
             ms = []
             for _ in range(3):
