@@ -893,6 +893,99 @@ clt256_words5_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #pragma pop_macro("CLT256V2_W_DRAIN")
 
 // ---------------------------------------------------------------------------
+// clt256_words6_kernel (knob words_variant = 6): words2 with the drain moved to its own warps.  The source page of
+// the words2 capture (profiles/r2_words2_ncu_full.txt) puts 59 % of its stall samples in the recurrence part of the
+// clock although that part holds only 2064 of the 5260 instructions: the 32 drain pieces woven into it (8 LDS ->
+// 2 STG each) expose the shared-memory latency at every store, and the next piece's loads wait for the scattered
+// stores to read their registers (long-scoreboard stalls on LOP3 / LDS), with one warp per scheduler and nobody to
+// hide either.  Here warps 0-3 run the clock and the transposes exactly as in words2, and warps 4-7 (255 registers
+// each as well: 256 x 255 fits the register file) copy stage -> HBM, four streams per batch.  Producer / consumer
+// hand-off per warp pair over two named barriers (full, empty), PTX bar.arrive / bar.sync with 64 participants; the
+// stage stays single-buffered (128 KB), so the drain overlaps the NEXT clock's recurrence and the transposes wait
+// for it.
+// ---------------------------------------------------------------------------
+#pragma push_macro("CLT256V2_W_DRAIN")
+#pragma push_macro("CLT256V2_W_BEGIN")
+#pragma push_macro("CLT256V2_W_END")
+#undef CLT256V2_W_DRAIN
+#undef CLT256V2_W_BEGIN
+#undef CLT256V2_W_END
+#define CLT256V2_W_DRAIN(j)
+#define CLT256V2_W_BEGIN                                                                                             \
+    if (it != 0u) asm volatile("bar.sync %0, 64;" ::"r"(bar_empty) : "memory");   /* clock it-1 has left the stage */ \
+    _Pragma("unroll 1") for (uint32_t w_ = 0; w_ < 8u; w_++) {                                                       \
+        uint32_t tw[32];                                                                                             \
+        switch (w_) {
+#define CLT256V2_W_END                                                                                               \
+        }                                                                                                            \
+        transpose32_fast(tw);                                                                                        \
+        const uint32_t sa = (w_ < 4u ? stage_a : stage_b) + w_ * (uint32_t)(CLT256V2_B * 4);                         \
+        _Pragma("unroll") for (int j = 0; j < 32; j++)                                                               \
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(sa + (uint32_t)(j * 8 * CLT256V2_B * 4)), "r"(tw[j]));      \
+    }                                                                                                                \
+    asm volatile("bar.arrive %0, 64;" ::"r"(bar_full) : "memory");
+
+__global__ void __launch_bounds__(2 * CLT256V2_B, 1)
+clt256_words6_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t stage_base = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
+    const uint32_t pair = (threadIdx.x >> 5) & 3u;                   // compute warp `pair` feeds drain warp 4 + `pair`
+    const uint32_t bar_full = 1u + pair, bar_empty = 5u + pair;      // barrier 0 is __syncthreads
+    if (threadIdx.x >= CLT256V2_B) {
+        // drain warp: lanes 2q, 2q+1 write the two 16-byte halves of one stream's clock (words2's store side)
+        const uint32_t lane = threadIdx.x & 31u, q = lane >> 1, h = lane & 1u;
+        const uint32_t u0 = pair * 32u + q, u1 = u0 + 16u;
+        const uint32_t rd0 = stage_base + ((4u * h) * CLT256V2_B + (u0 ^ (16u * h))) * 4u;
+        const uint32_t rd1 = stage_base + ((4u * h) * CLT256V2_B + (u1 ^ (16u * h))) * 4u;
+        uint32_t *const op0 = out + (size_t)(blockIdx.x * CLT256V2_B + u0) * 32u * L * 8u + 4u * h;
+        uint32_t *const op1 = out + (size_t)(blockIdx.x * CLT256V2_B + u1) * 32u * L * 8u + 4u * h;
+#pragma unroll 1
+        for (uint32_t it = 0; it < L; it++) {
+            asm volatile("bar.sync %0, 64;" ::"r"(bar_full) : "memory");
+#pragma unroll 2
+            for (uint32_t jb = 0; jb < 32u; jb += 4u) {
+                uint32_t v[4][8];
+#pragma unroll
+                for (uint32_t jj = 0; jj < 4u; jj++)
+#pragma unroll
+                    for (uint32_t i = 0; i < 4u; i++) {
+                        const uint32_t o = ((jb + jj) * 8u + i) * (uint32_t)(CLT256V2_B * 4);
+                        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[jj][i]) : "r"(rd0 + o));
+                        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[jj][4 + i]) : "r"(rd1 + o));
+                    }
+#pragma unroll
+                for (uint32_t jj = 0; jj < 4u; jj++) {
+                    const size_t off = ((size_t)(jb + jj) * L + it) * 8u;
+                    CLT256V2W_STORE((uint4 *)(op0 + off), make_uint4(v[jj][0], v[jj][1], v[jj][2], v[jj][3]));
+                    CLT256V2W_STORE((uint4 *)(op1 + off), make_uint4(v[jj][4], v[jj][5], v[jj][6], v[jj][7]));
+                }
+            }
+            if (it + 1u < L) asm volatile("bar.arrive %0, 64;" ::"r"(bar_empty) : "memory");
+        }
+        return;
+    }
+    const uint32_t tid = threadIdx.x;
+    const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+    uint32_t *const st = (uint32_t *)smem4 + tid;
+    for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+    const uint32_t stage_a = stage_base + tid * 4u, stage_b = stage_base + (tid ^ 16u) * 4u;
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+    for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_W_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_W_BODY
+    }
+}
+#pragma pop_macro("CLT256V2_W_END")
+#pragma pop_macro("CLT256V2_W_BEGIN")
+#pragma pop_macro("CLT256V2_W_DRAIN")
+
+// ---------------------------------------------------------------------------
 // clt256_words3_kernel (EXPERIMENT, knob "words_b192"; measured and rejected): the same clock and transposes with
 // SIX warps per SM instead of four.  ncu on words2 shows neither pipe busy (ALU 34 %, LSU 36 %), so more warps
 // looked like the fix; but 192 threads need 114 KB of state, which leaves room for only HALF a clock of staging
@@ -995,6 +1088,10 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
                                                                              (int32_t)noise_var);
         c->last_kernel = "clt256_s16";
+    } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 6) {
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_words6_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2W_SMEM));
+        clt256_words6_kernel<<<blocks, 2 * CLT256V2_B, CLT256V2W_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
+        c->last_kernel = "clt256_words6";
     } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 5) {
         const uint32_t T = blocks * CLT256V2_B;
         uint32_t *slab = (uint32_t *)c->scratch(11, (size_t)256 * T * 4);

@@ -6,6 +6,8 @@ ctx = lib.Context(0)
 ctx.lutopt_load_shipped(256)
 n = 1 << 28
 buf = torch.empty(n * 4, dtype=torch.int64, device="cuda")
+variant = int(os.environ.get("WORDS_VARIANT", "0"))
+ctx.set_tuning("words_variant", variant)
 for blocks in (148, 111, 74, 37, 148):
     ctx.set_tuning("clt_spec_max_blocks", blocks)
     for rep in range(2):
