@@ -258,6 +258,9 @@ int bbb_create(int device, bbb_ctx **out)
     c->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_tail_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_tail_join, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_slot[0], cudaEventDisableTiming) != cudaSuccess ||
@@ -279,6 +282,10 @@ void bbb_destroy(bbb_ctx *c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->stream2) cudaStreamSynchronize(c->stream2);
+    if (c->stream3) cudaStreamSynchronize(c->stream3);
+    if (c->ev_tail_fork) cudaEventDestroy(c->ev_tail_fork);
+    if (c->ev_tail_join) cudaEventDestroy(c->ev_tail_join);
+    if (c->stream3) cudaStreamDestroy(c->stream3);
     for (int i = 0; i < 16; i++) if (c->d_scratch[i]) cudaFree(c->d_scratch[i]);
     for (int i = 0; i < 4; i++) if (c->h_pinned[i]) cudaFreeHost(c->h_pinned[i]);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);

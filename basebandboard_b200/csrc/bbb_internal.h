@@ -37,6 +37,8 @@ struct bbb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;    // second queue: overlapped batches (rnghunt) and chunked D2H copies (streams)
+    cudaStream_t stream3 = nullptr;    // third queue: the ragged tail of a CLT / word-stream call beside its main launch
+    cudaEvent_t ev_tail_fork = nullptr, ev_tail_join = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evt0 = nullptr, evt1 = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_slot[2] = {nullptr, nullptr}, ev_aux[2] = {nullptr, nullptr};
     uint64_t h2d_bytes = 0, d2h_bytes = 0;

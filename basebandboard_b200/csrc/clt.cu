@@ -256,6 +256,7 @@ static int launch_seed(bbb_ctx *c, const uint32_t *dJ, const SeedStart &xs, uint
 // clt_spec.cu
 int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only);
 int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c, int kind);
+uint32_t bbb_clt_spec_wave_blocks(const bbb_ctx *c, int kind);
 int bbb_clt_spec_words_streams_per_block(const bbb_ctx *c);
 int bbb_clt_spec_launch(bbb_ctx *c, uint32_t blocks, uint32_t L, uint32_t model, const uint32_t *planes,
                         unsigned long long *hist);
@@ -366,15 +367,39 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
     else if (kind == 2 && bbb_clt_spec_stream_ok(c, kind)) spb = (uint64_t)bbb_clt_spec_words_streams_per_block(c);
     else if (kind > 0 && bbb_clt_spec_stream_ok(c, kind)) spb = (uint64_t)bbb_clt_spec_streams_per_block(c, true);
 
+    // The pieces after a straight-line launch (its ragged tail: a seeding kernel + a short data-driven launch, 0.2 ms
+    // beside a 3 ms word-stream kernel) are independent of it: they run on ctx->stream3 with their own plane buffer
+    // and join the call's stream at the end.
+    struct TailFork {
+        bbb_ctx *c;
+        cudaStream_t main;
+        bool forked = false;
+        ~TailFork()
+        {
+            c->stream = main;
+            if (forked && cudaEventRecord(c->ev_tail_join, c->stream3) == cudaSuccess)
+                cudaStreamWaitEvent(main, c->ev_tail_join, 0);
+        }
+    } fork{c, c->stream};
+    BBB_CUDA(c, cudaEventRecord(c->ev_tail_fork, fork.main));
+    uint64_t tail_below = 0;             // streams of the last straight-line launch: what is left after it is < this
+
     uint64_t done = 0;
     c->last_kernel = "generic";
     while (done < count) {
         const uint64_t rem = count - done;
+        if (tail_below && rem < tail_below && !fork.forked) {
+            BBB_CUDA(c, cudaStreamWaitEvent(c->stream3, c->ev_tail_fork, 0));
+            c->stream = c->stream3;
+            fork.forked = true;
+        }
+        const int planes_slot = fork.forked ? 15 : 1;
 
         // ---- specialised kernel: `blocks` CTAs x spb streams x L clocks, one wave ----
-        if (spb && ((kind != 1 && kind != 3) || (done & 31) == 0)) {
+        if (spb && !fork.forked && ((kind != 1 && kind != 3) || (done & 31) == 0)) {   // (the tail: data-driven only,
+                                                                                       // the slabs of the stream kernels are in use)
             const uint64_t max_blocks = c->tune_spec_max_blocks ? c->tune_spec_max_blocks
-                                        : (uint64_t)c->sm_count * bbb_clt_spec_blocks_per_sm(c, kind);
+                                        : (uint64_t)bbb_clt_spec_wave_blocks(c, kind);
             // fewest clocks per stream worth a launch (the stream kernels amortise their seeding sooner)
             const uint64_t min_steps = kind == 2   ? (c->tune_spec_min_steps / 4 > 8 ? c->tune_spec_min_steps / 4 : 8)
                                        : kind > 0 ? (c->tune_spec_min_steps / 4 > 32 ? c->tune_spec_min_steps / 4 : 32)
@@ -391,7 +416,7 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
                 while (nbits < 40 && ((S - 1) >> nbits)) nbits++;
                 uint32_t *dJ = upload_jump_ops(c, L, nbits);
                 if (!dJ) return BBB_ECUDA;
-                uint32_t *d_planes = (uint32_t *)c->scratch(1, (size_t)n * T * 4);
+                uint32_t *d_planes = (uint32_t *)c->scratch(planes_slot, (size_t)n * T * 4);
                 if (!d_planes) return BBB_ECUDA;
                 // the CLT kernels take the tree of a stream's state BEFORE each clock: start one clock in;
                 // the raw-word kernel emits the state AFTER each clock
@@ -412,6 +437,7 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
                                                                 : (void *)(d_out_words32 + done * 8),
                                                     noise_var);
                 if (rc) return rc;
+                tail_below = S;
                 advance_state(c, xl, S * L);
                 done += S * L;
                 continue;
@@ -436,7 +462,7 @@ int bbb_clt_run_device(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t 
         while (nbits < 40 && ((S - 1) >> nbits)) nbits++;
         uint32_t *dJ = upload_jump_ops(c, L, nbits);
         if (!dJ) return BBB_ECUDA;
-        uint32_t *d_planes = (uint32_t *)c->scratch(1, (size_t)n * T * 4);
+        uint32_t *d_planes = (uint32_t *)c->scratch(planes_slot, (size_t)n * T * 4);
         if (!d_planes) return BBB_ECUDA;
         SeedStart xs;
         to_seed(xl, nw64, xs);

@@ -236,6 +236,23 @@ int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c, int kind)
     return c->tune_spec_variant == 1 ? 1 : CLT256V2_CTAS_PER_SM;
 }
 
+// CTAs of one wave of a straight-line launch.  The raw-word kernel (clt256_words7_kernel) is the exception to "fill
+// every SM": each CTA keeps 4096 streams open and a stream's 128-byte line stays in L2 for four clocks, so the open
+// lines of 148 CTAs (78 MB) no longer fit beside each other and leave as single sectors; 128 CTAs (2^19 streams,
+// 64 MB) run the same kernel 1.27 times faster (2859 against 2255 GB/s, profiles/r2_probe_words7.txt): the largest
+// power of two that uses at least 3/4 of the SMs (a power-of-two stream count also leaves 2^k-step calls without a
+// ragged tail), else 7/8 of them.
+uint32_t bbb_clt_spec_wave_blocks(const bbb_ctx *c, int kind)
+{
+    const uint32_t sms = (uint32_t)c->sm_count;
+    const bool words7 = kind == 2 && c->tune_spec_variant != 1 && !c->tune_words_b192 &&
+                        (c->tune_words_variant == 0 || c->tune_words_variant == 7 || c->tune_words_variant == 8);
+    if (!words7) return sms * (uint32_t)bbb_clt_spec_blocks_per_sm(c, kind);
+    uint32_t p2 = 1;
+    while (p2 * 2 <= sms) p2 *= 2;
+    return p2 * 4 >= sms * 3 ? p2 : sms * 7 / 8;
+}
+
 // Streams one CTA carries, and whether the loaded recurrence has a specialised kernel.
 int bbb_clt_spec_streams_per_block(const bbb_ctx *c, bool hist_only)
 {
@@ -652,6 +669,11 @@ __device__ __forceinline__ void st_evict_last(uint4 *p, uint4 v)
 }
 #define CLT256V2W_STORE(p, v) st_evict_last(p, v)
 #endif
+__device__ __forceinline__ void st_policy(uint4 *p, uint4 v, uint64_t pol)
+{
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w),
+                 "l"(pol) : "memory");
+}
 
 __global__ void __launch_bounds__(CLT256V2_B, 1)
 clt256_words2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
@@ -986,6 +1008,170 @@ clt256_words6_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #pragma pop_macro("CLT256V2_W_DRAIN")
 
 // ---------------------------------------------------------------------------
+// clt256_words7_kernel (knob words_variant = 7): the stage lives in TENSOR MEMORY.  A thread's un-sliced clock is
+// 256 words; TMEM gives every lane of the four compute warps 512 private columns (128 lanes x 512 columns x 4 B =
+// 256 KB per SM, reachable only with tcgen05.ld / tcgen05.st), i.e. exactly two clocks per thread -- the double
+// buffer that shared memory has no room for (state 76 KB + one 128 KB stage).  Warps 0-3 run the clock and the
+// eight 32x32 transposes as in words2, but a transposed word leaves its 32 registers with ONE
+// tcgen05.st.32x32b.x32 (column = buffer*256 + word*32 + stream) instead of 32 st.shared; warps 4-7 sit on the same
+// TMEM lane quarters (warp id mod 4), read eight streams x eight words at a time (tcgen05.ld.32x32b.x8) and store
+// the 32-byte clocks.  The drain of clock `it` overlaps the WHOLE clock it+1 (words6 could only use its recurrence
+// phase), and the 512 shared-memory accesses per thread and clock of the stage are gone from the LSU pipe.
+// Hand-off per warp pair and buffer: mbarrier full / empty (32 arrivals each), tcgen05 fences around them.
+// ---------------------------------------------------------------------------
+#define CLT256V7_CTRL_BYTES 256
+#define CLT256V7_SMEM (CLT256V2_STATE_BYTES + CLT256V7_CTRL_BYTES)
+
+__device__ __forceinline__ void mbar_init(uint32_t a, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t a)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(a) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t a, uint32_t parity)
+{
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "W7_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra W7_DONE;\n"
+                 "bra W7_WAIT;\n"
+                 "W7_DONE:\n"
+                 "}" ::"r"(a), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32])
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, "
+                 "%15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+                 "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+                 "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+                 "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+                 "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr) : "memory");
+}
+
+#pragma push_macro("CLT256V2_W_DRAIN")
+#pragma push_macro("CLT256V2_W_BEGIN")
+#pragma push_macro("CLT256V2_W_END")
+#undef CLT256V2_W_DRAIN
+#undef CLT256V2_W_BEGIN
+#undef CLT256V2_W_END
+#define CLT256V2_W_DRAIN(j)
+#define CLT256V2_W_BEGIN                                                                                             \
+    const uint32_t b_ = it & 1u, k_ = it >> 1;                                                                       \
+    if (k_ != 0u) {                      /* the drain warp has read use k_-1 of this buffer */                        \
+        mbar_wait(bar_empty + 8u * b_, (k_ - 1u) & 1u);                                                              \
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");                                              \
+    }                                                                                                                \
+    _Pragma("unroll 1") for (uint32_t w_ = 0; w_ < 8u; w_++) {                                                       \
+        uint32_t tw[32];                                                                                             \
+        switch (w_) {
+#define CLT256V2_W_END                                                                                               \
+        }                                                                                                            \
+        transpose32_fast(tw);                                                                                        \
+        tmem_st32(taddr + b_ * 256u + w_ * 32u, tw);                                                                 \
+    }                                                                                                                \
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");                                                     \
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");                                                 \
+    mbar_arrive(bar_full + 8u * b_);
+
+// POLICY2 = 0 (knob words_variant = 8) stores every sector with evict_last, as words2 does.
+template <int POLICY2>
+__global__ void __launch_bounds__(2 * CLT256V2_B, 1)
+clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t ctrl = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
+    const uint32_t warp = threadIdx.x >> 5, pair = warp & 3u, lane = threadIdx.x & 31u;
+    if (warp == 4u) {                    // one warp allocates all 512 columns (one CTA per SM)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(ctrl + 128u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (threadIdx.x == 0)
+        for (uint32_t i = 0; i < 16u; i++) mbar_init(ctrl + 8u * i, 32u);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tbase = *(const volatile uint32_t *)((const char *)smem4 + CLT256V2_STATE_BYTES + 128);
+    const uint32_t taddr = tbase + ((pair * 32u) << 16);              // this warp's lane quarter, column 0
+    const uint32_t bar_full = ctrl + pair * 32u, bar_empty = bar_full + 16u;   // [buffer] 8 bytes apart
+    if (warp >= 4u) {
+        // lanes 2q, 2q+1 swap halves by shuffle so that a warp store covers 16 complete sectors (words2's store side; every
+        // lane storing its own thread's two halves -- 32 half sectors per warp store -- ran at HALF the speed: 434 against
+        // 892 GB/s on 37 CTAs): the even lane of a pair keeps the low halves (words 0-3) of both threads, the odd lane the
+        // high ones
+        const uint32_t odd = lane & 1u;
+        uint32_t *const opa = out + (size_t)(blockIdx.x * CLT256V2_B + pair * 32u + (lane & ~1u)) * 32u * L * 8u + 4u * odd;
+        uint32_t *const opb = opa + (size_t)32u * L * 8u;                 // the odd thread's streams
+        // a stream's 128-byte line fills over four clocks: the first three sectors ask L2 to keep the line
+        // (evict_last), the completing one releases it (evict_first), so only partial lines compete for residency
+        uint64_t pol_keep, pol_done;
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_done));
+#pragma unroll 1
+        for (uint32_t it = 0; it < L; it++) {
+            const uint32_t b = it & 1u, k = it >> 1;
+            mbar_wait(bar_full + 8u * b, k & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+            for (uint32_t jb = 0; jb < 32u; jb += 8u) {
+                uint32_t v[8][8];
+#pragma unroll
+                for (uint32_t w = 0; w < 8u; w++) tmem_ld8(taddr + b * 256u + w * 32u + jb, v[w]);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (uint32_t jj = 0; jj < 8u; jj++) {
+                        uint32_t keep[4], got[4];
+#pragma unroll
+                        for (uint32_t i = 0; i < 4u; i++) {
+                            keep[i] = odd ? v[4 + i][jj] : v[i][jj];
+                            got[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i][jj] : v[4 + i][jj], 1);
+                        }
+                        const uint32_t sec = (jb + jj) * L + it;          // sector number within the thread's 32 streams
+                        const size_t off = (size_t)sec * 8u;
+                        const uint64_t pol = POLICY2 && (sec & 3u) == 3u ? pol_done : pol_keep;
+                        // first store: the even thread's stream (even lane: its own low half, odd lane: the received high half)
+                        st_policy((uint4 *)(opa + off), odd ? make_uint4(got[0], got[1], got[2], got[3])
+                                                            : make_uint4(keep[0], keep[1], keep[2], keep[3]), pol);
+                        st_policy((uint4 *)(opb + off), odd ? make_uint4(keep[0], keep[1], keep[2], keep[3])
+                                                            : make_uint4(got[0], got[1], got[2], got[3]), pol);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(bar_empty + 8u * b);
+        }
+    } else {
+        const uint32_t tid = threadIdx.x;
+        const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+        uint32_t *const st = (uint32_t *)smem4 + tid;
+        for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+        for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_W_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_W_BODY
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 4u) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
+}
+#pragma pop_macro("CLT256V2_W_END")
+#pragma pop_macro("CLT256V2_W_BEGIN")
+#pragma pop_macro("CLT256V2_W_DRAIN")
+
+// ---------------------------------------------------------------------------
 // clt256_words3_kernel (EXPERIMENT, knob "words_b192"; measured and rejected): the same clock and transposes with
 // SIX warps per SM instead of four.  ncu on words2 shows neither pipe busy (ALU 34 %, LSU 36 %), so more warps
 // looked like the fix; but 192 threads need 114 KB of state, which leaves room for only HALF a clock of staging
@@ -1109,6 +1295,11 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V3W_SMEM));
         clt256_words3_kernel<<<blocks, 192, CLT256V3W_SMEM, c->stream>>>(planes, blocks * 192, L, (uint32_t *)out);
         c->last_kernel = "clt256_words3";
+    } else if (c->tune_spec_variant != 1 && c->tune_words_variant != 2) {
+        auto kern = c->tune_words_variant == 8 ? clt256_words7_kernel<0> : clt256_words7_kernel<1>;
+        BBB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V7_SMEM));
+        kern<<<blocks, 2 * CLT256V2_B, CLT256V7_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
+        c->last_kernel = "clt256_words7";
     } else if (c->tune_spec_variant != 1) {
         static_assert(CLT256V2W_SMEM <= 227 * 1024, "shared memory budget");
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2W_SMEM));

@@ -22,7 +22,7 @@ c.tx_stream(31, 1 << 25, shaper.tx_sets()[16], dev_ptr=buf.data_ptr())    # shap
 c.sync()
 c.prbs_shaped_slicer_detect(31, 1 << 22, shaper.tx_sets()[16], noise_var=15, delay=4)   # shaped_slicer_err_kernel + detector on error words
 c.sync()
-c.lutopt_stream_dev(1, 0, 148 * 4096 * 32, buf.data_ptr())                # clt256_words2_kernel (32 clocks x 32 B x 606k streams)
+c.lutopt_stream_dev(1, 0, 148 * 4096 * 32, buf.data_ptr())                # clt256_words7_kernel (2^19 streams, 36 clocks x 32 B)
 c.sync()
 print("ok", c.last_kernel)
 c.close()

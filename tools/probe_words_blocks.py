@@ -8,7 +8,7 @@ n = 1 << 28
 buf = torch.empty(n * 4, dtype=torch.int64, device="cuda")
 variant = int(os.environ.get("WORDS_VARIANT", "0"))
 ctx.set_tuning("words_variant", variant)
-for blocks in (148, 111, 74, 37, 148):
+for blocks in [int(x) for x in os.environ.get("BLOCKS", "148,111,74,37,148").split(",")]:
     ctx.set_tuning("clt_spec_max_blocks", blocks)
     for rep in range(2):
         ctx.lutopt_stream_dev(1, 0, n, buf.data_ptr()); ctx.sync()
