@@ -335,6 +335,9 @@ def test_spec256_streams_equal_generic_large(ctx):
     try:
         ctx.lutopt_stream_dev(1, 5, wc, wa.data_ptr())
         ctx.sync()
+        # the product path: 128 CTAs of clt256_words7 (tensor-memory stage), 74 clocks (not a multiple of the four
+        # sectors of a line), ragged tail on the third stream
+        assert ctx.last_kernel == "clt256_words7" and ctx.last_launches == 4
         ctx.set_tuning("clt_no_spec", 1)
         ctx.lutopt_stream_dev(1, 5, wc, wb.data_ptr())
         ctx.sync()
