@@ -246,7 +246,7 @@ uint32_t bbb_clt_spec_wave_blocks(const bbb_ctx *c, int kind)
 {
     const uint32_t sms = (uint32_t)c->sm_count;
     const bool words7 = kind == 2 && c->tune_spec_variant != 1 && !c->tune_words_b192 &&
-                        (c->tune_words_variant == 0 || c->tune_words_variant == 7 || c->tune_words_variant == 8);
+                        (c->tune_words_variant == 0 || c->tune_words_variant >= 7);
     if (!words7) return sms * (uint32_t)bbb_clt_spec_blocks_per_sm(c, kind);
     uint32_t p2 = 1;
     while (p2 * 2 <= sms) p2 *= 2;
@@ -1050,6 +1050,17 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
                  "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
                  "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]) : "memory");
 }
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, "
+                 "%15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                   "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+                   "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+                   "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr) : "memory");
+}
+
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8])
 {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
@@ -1075,7 +1086,7 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8])
         switch (w_) {
 #define CLT256V2_W_END                                                                                               \
         }                                                                                                            \
-        transpose32_fast(tw);                                                                                        \
+        if (!W7_SPLIT || w_ < 4u) transpose32_fast(tw);   /* SPLIT: words 4-7 go to TMEM bit-sliced */                 \
         tmem_st32(taddr + b_ * 256u + w_ * 32u, tw);                                                                 \
     }                                                                                                                \
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");                                                     \
@@ -1083,10 +1094,14 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8])
     mbar_arrive(bar_full + 8u * b_);
 
 // POLICY2 = 0 (knob words_variant = 8) stores every sector with evict_last, as words2 does.
-template <int POLICY2>
+// SPLIT = 1: the compute warps transpose only words 0-3 of a clock and store the planes of words 4-7 as they are; the
+// drain warps transpose those four words themselves (tcgen05.ld.x32 + 32x32 register transposes), so that the two warps
+// of a scheduler carry about the same number of instructions per clock (2350 / 2000 instead of 4500 / 600).
+template <int POLICY2, int SPLIT>
 __global__ void __launch_bounds__(2 * CLT256V2_B, 1)
 clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
 {
+    constexpr bool W7_SPLIT = SPLIT != 0;
     extern __shared__ uint4 smem4[];
     const uint32_t ctrl = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
     const uint32_t warp = threadIdx.x >> 5, pair = warp & 3u, lane = threadIdx.x & 31u;
@@ -1120,6 +1135,37 @@ clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
             const uint32_t b = it & 1u, k = it >> 1;
             mbar_wait(bar_full + 8u * b, k & 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (W7_SPLIT) {
+                uint32_t tq[4][32];                                    // words 4-7: planes in, [word][stream] out
+#pragma unroll
+                for (uint32_t w = 0; w < 4u; w++) tmem_ld32(taddr + b * 256u + 128u + w * 32u, tq[w]);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (uint32_t w = 0; w < 4u; w++) transpose32_fast(tq[w]);
+#pragma unroll
+                for (uint32_t jb = 0; jb < 32u; jb += 8u) {
+                    uint32_t v[4][8];                                  // words 0-3 of streams jb .. jb+7
+#pragma unroll
+                    for (uint32_t w = 0; w < 4u; w++) tmem_ld8(taddr + b * 256u + w * 32u + jb, v[w]);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                    for (uint32_t jj = 0; jj < 8u; jj++) {
+                        uint32_t keep[4], got[4];
+#pragma unroll
+                        for (uint32_t i = 0; i < 4u; i++) {
+                            keep[i] = odd ? tq[i][jb + jj] : v[i][jj];
+                            got[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i][jj] : tq[i][jb + jj], 1);
+                        }
+                        const uint32_t sec = (jb + jj) * L + it;
+                        const size_t off = (size_t)sec * 8u;
+                        const uint64_t pol = POLICY2 && (sec & 3u) == 3u ? pol_done : pol_keep;
+                        st_policy((uint4 *)(opa + off), odd ? make_uint4(got[0], got[1], got[2], got[3])
+                                                            : make_uint4(keep[0], keep[1], keep[2], keep[3]), pol);
+                        st_policy((uint4 *)(opb + off), odd ? make_uint4(keep[0], keep[1], keep[2], keep[3])
+                                                            : make_uint4(got[0], got[1], got[2], got[3]), pol);
+                    }
+                }
+            } else
 #pragma unroll 1
             for (uint32_t jb = 0; jb < 32u; jb += 8u) {
                 uint32_t v[8][8];
@@ -1142,6 +1188,136 @@ clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
                                                             : make_uint4(keep[0], keep[1], keep[2], keep[3]), pol);
                         st_policy((uint4 *)(opb + off), odd ? make_uint4(keep[0], keep[1], keep[2], keep[3])
                                                             : make_uint4(got[0], got[1], got[2], got[3]), pol);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(bar_empty + 8u * b);
+        }
+    } else {
+        const uint32_t tid = threadIdx.x;
+        const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+        uint32_t *const st = (uint32_t *)smem4 + tid;
+        for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+        for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_W_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_W_BODY
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 4u) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
+}
+#pragma pop_macro("CLT256V2_W_END")
+#pragma pop_macro("CLT256V2_W_BEGIN")
+#pragma pop_macro("CLT256V2_W_DRAIN")
+
+// ---------------------------------------------------------------------------
+// clt256_words8_kernel (knob words_variant = 9): words7 with the UN-SLICING moved to the drain warps as well.  In
+// words7 a scheduler holds one compute warp with 4500 instructions per clock (recurrence 1600 + transposes 2400 +
+// the rest) and one drain warp with 600: the compute warp alone cannot issue more than every other cycle (53 % of the
+// slots).  Here the compute warps hand the NEW STATE to tensor memory as it is, bit-sliced (the 32 planes of word w
+// with one tcgen05.st.x32, column = buffer*256 + word*32 + plane), and a drain warp reads them back four times, once
+// per group of 8 streams: byte g of the 32 planes of a word gathered with 24 PRMT, an 8x8 bit transpose in three
+// shift/LOP3 stages (unslice8 of words4), eight words -> 8 streams x 32 bytes in 64 registers, lane pairs, stores.
+// Per clock about 1900 instructions on the compute warp and 3300 on the drain warp of the same scheduler.
+// ---------------------------------------------------------------------------
+#pragma push_macro("CLT256V2_W_DRAIN")
+#pragma push_macro("CLT256V2_W_BEGIN")
+#pragma push_macro("CLT256V2_W_END")
+#undef CLT256V2_W_DRAIN
+#undef CLT256V2_W_BEGIN
+#undef CLT256V2_W_END
+#define CLT256V2_W_DRAIN(j)
+#define CLT256V2_W_BEGIN                                                                                             \
+    const uint32_t b_ = it & 1u, k_ = it >> 1;                                                                       \
+    if (k_ != 0u) {                      /* the drain warp has read use k_-1 of this buffer */                        \
+        mbar_wait(bar_empty + 8u * b_, (k_ - 1u) & 1u);                                                              \
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");                                              \
+    }                                                                                                                \
+    _Pragma("unroll 1") for (uint32_t w_ = 0; w_ < 8u; w_++) {                                                       \
+        uint32_t tw[32];                                                                                             \
+        switch (w_) {
+#define CLT256V2_W_END                                                                                               \
+        }                                                                                                            \
+        tmem_st32(taddr + b_ * 256u + w_ * 32u, tw);                                                                 \
+    }                                                                                                                \
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");                                                     \
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");                                                 \
+    mbar_arrive(bar_full + 8u * b_);
+
+__global__ void __launch_bounds__(2 * CLT256V2_B, 1)
+clt256_words8_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t ctrl = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
+    const uint32_t warp = threadIdx.x >> 5, pair = warp & 3u, lane = threadIdx.x & 31u;
+    if (warp == 4u) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(ctrl + 128u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (threadIdx.x == 0)
+        for (uint32_t i = 0; i < 16u; i++) mbar_init(ctrl + 8u * i, 32u);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tbase = *(const volatile uint32_t *)((const char *)smem4 + CLT256V2_STATE_BYTES + 128);
+    const uint32_t taddr = tbase + ((pair * 32u) << 16);
+    const uint32_t bar_full = ctrl + pair * 32u, bar_empty = bar_full + 16u;
+    if (warp >= 4u) {
+        const uint32_t odd = lane & 1u;
+        uint32_t *const opa = out + (size_t)(blockIdx.x * CLT256V2_B + pair * 32u + (lane & ~1u)) * 32u * L * 8u + 4u * odd;
+        uint32_t *const opb = opa + (size_t)32u * L * 8u;
+        uint64_t pol_keep, pol_done;
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_done));
+#pragma unroll 1
+        for (uint32_t it = 0; it < L; it++) {
+            const uint32_t b = it & 1u, k = it >> 1;
+            mbar_wait(bar_full + 8u * b, k & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            // software pipeline over the 16 (group, word pair) steps of a clock: the planes of the next step are on their
+            // way from TMEM while this step's are un-sliced (tcgen05.wait::ld waits for every load issued, so the next
+            // load is issued right after the wait)
+            uint32_t ta[2][32], tb[2][32];
+            const uint32_t tcol = taddr + b * 256u;
+            tmem_ld32(tcol, ta[0]);
+            tmem_ld32(tcol + 32u, tb[0]);
+#pragma unroll 1
+            for (uint32_t g = 0; g < 4u; g++) {
+                const uint32_t sel2 = g | ((4u + g) << 4);
+                uint32_t v[8][8];                                      // [word][stream of the group]
+#pragma unroll
+                for (uint32_t p = 0; p < 4u; p++) {                    // words 2p, 2p+1
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (p < 3u || g < 3u) {
+                        const uint32_t nw = p < 3u ? 2u * (p + 1u) : 0u;
+                        tmem_ld32(tcol + nw * 32u, ta[(p + 1u) & 1u]);
+                        tmem_ld32(tcol + nw * 32u + 32u, tb[(p + 1u) & 1u]);
+                    }
+                    unslice8(ta[p & 1u], sel2, v[2u * p]);
+                    unslice8(tb[p & 1u], sel2, v[2u * p + 1u]);
+                }
+#pragma unroll
+                for (uint32_t jj = 0; jj < 8u; jj++) {
+                    uint32_t keep[4], got[4];
+#pragma unroll
+                    for (uint32_t i = 0; i < 4u; i++) {
+                        keep[i] = odd ? v[4 + i][jj] : v[i][jj];
+                        got[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i][jj] : v[4 + i][jj], 1);
+                    }
+                    const uint32_t sec = (g * 8u + jj) * L + it;
+                    const size_t off = (size_t)sec * 8u;
+                    const uint64_t pol = (sec & 3u) == 3u ? pol_done : pol_keep;
+                    st_policy((uint4 *)(opa + off), odd ? make_uint4(got[0], got[1], got[2], got[3])
+                                                        : make_uint4(keep[0], keep[1], keep[2], keep[3]), pol);
+                    st_policy((uint4 *)(opb + off), odd ? make_uint4(keep[0], keep[1], keep[2], keep[3])
+                                                        : make_uint4(got[0], got[1], got[2], got[3]), pol);
                 }
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -1274,6 +1450,10 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
                                                                              (int32_t)noise_var);
         c->last_kernel = "clt256_s16";
+    } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 9) {
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_words8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V7_SMEM));
+        clt256_words8_kernel<<<blocks, 2 * CLT256V2_B, CLT256V7_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
+        c->last_kernel = "clt256_words8";
     } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 6) {
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words6_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2W_SMEM));
         clt256_words6_kernel<<<blocks, 2 * CLT256V2_B, CLT256V2W_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
@@ -1296,7 +1476,8 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_words3_kernel<<<blocks, 192, CLT256V3W_SMEM, c->stream>>>(planes, blocks * 192, L, (uint32_t *)out);
         c->last_kernel = "clt256_words3";
     } else if (c->tune_spec_variant != 1 && c->tune_words_variant != 2) {
-        auto kern = c->tune_words_variant == 8 ? clt256_words7_kernel<0> : clt256_words7_kernel<1>;
+        auto kern = c->tune_words_variant == 8 ? clt256_words7_kernel<0, 0>
+                    : c->tune_words_variant == 10 ? clt256_words7_kernel<1, 1> : clt256_words7_kernel<1, 0>;
         BBB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V7_SMEM));
         kern<<<blocks, 2 * CLT256V2_B, CLT256V7_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
         c->last_kernel = "clt256_words7";

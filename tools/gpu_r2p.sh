@@ -1,4 +1,3 @@
 set -x
-mkdir -p gpurun_out/r2s
-timeout 2400 python -m pytest tests -x -q -m gpu 2>&1 | tail -5 | tee gpurun_out/r2s/pytest_gpu.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -3 | tee gpurun_out/r2s/smoke.log
+mkdir -p gpurun_out/r2u
+BLOCKS=148,140,136,132,128,124,120,112,104,96,128 WORDS_VARIANT=0 timeout 120 python tools/probe_words_blocks.py 2>&1 | tee gpurun_out/r2u/probe_words7_sweep2.txt
