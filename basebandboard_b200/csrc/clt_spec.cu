@@ -116,6 +116,8 @@ clt256_hist_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, 
 #define CLT256V2_SMEM (CLT256V2_STATE_BYTES + CLT256_FAST_BYTES + CLT256V2_SLOW_WORDS * 4)
 #define CLT256V2_CTAS_PER_SM 2                        // 2 x (state + bins + 1 KB) <= 228 KB, 2 x 128 x 254 registers
 
+// (a & m) | (b & ~m), m a literal: one LOP3 (clt_common.cuh)
+#define CLT256V2_BSEL(m, a, b) bit_select<m>((a), (b))
 #define CLT256V2_SECTION_PERM
 #include "clt256_v2_gen.inc"
 #undef CLT256V2_SECTION_PERM

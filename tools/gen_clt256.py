@@ -268,7 +268,7 @@ def rmw_hooks(words, first_slot=0):
     return hooks
 
 
-def gen_transpose(em, q, out="z%d", decl="", shr=None):
+def gen_transpose(em, q, out="z%d", decl="", shr=None, bsel=None):
     """8x8 bit-block transpose of up to 8 planes q[0..] (missing ones are 0): on return byte m of
     word s holds the value (bit b = plane b) of stream 8m+s.  Writes out % s for s = 0..7."""
     x = list(q) + ["0u"] * (8 - len(q))
@@ -279,9 +279,17 @@ def gen_transpose(em, q, out="z%d", decl="", shr=None):
                 continue
             lo, hi = x[i], x[i + sh]
             nl, nh = em.tmp(), em.tmp()
-            em.emit("const uint32_t %s = (%s & %s) | ((%s & %s) << %d);" % (nl, lo, mask, hi, mask, sh))
             sh_lo = (shr % (lo, sh)) if shr else "(%s >> %d)" % (lo, sh)
-            em.emit("const uint32_t %s = (%s & %s) | (%s & ~%s);" % (nh, sh_lo, mask, hi, mask))
+            if bsel and hi != "0u":
+                # (a & m) | (b & ~m) as one LOP3 with the mask as its immediate (nvcc emits two for the C form)
+                em.emit("const uint32_t %s = %s;" % (nl, bsel % (mask, lo, "(%s << %d)" % (hi, sh))))
+                em.emit("const uint32_t %s = %s;" % (nh, bsel % (mask, sh_lo, hi)))
+            elif bsel:
+                em.emit("const uint32_t %s = %s & %s;" % (nl, lo, mask))
+                em.emit("const uint32_t %s = %s & %s;" % (nh, sh_lo, mask))
+            else:
+                em.emit("const uint32_t %s = (%s & %s) | ((%s & %s) << %d);" % (nl, lo, mask, hi, mask, sh))
+                em.emit("const uint32_t %s = (%s & %s) | (%s & ~%s);" % (nh, sh_lo, mask, hi, mask))
             y[i], y[i + sh] = nl, nh
         x = y
     for s in range(8):

@@ -134,7 +134,8 @@ def tail_lines(shape, kind="hist"):
         em.emit("const uint32_t pc%d = %s;" % (wgt, planes[wgt]))
     if kind == "s8":
         em.emit("const uint32_t pc7n = ~pc7;")
-        gen_transpose(em, ["pc0", "pc1", "pc2", "pc3", "pc4", "pc5", "pc6", "pc7n"], decl="const uint32_t ")
+        gen_transpose(em, ["pc0", "pc1", "pc2", "pc3", "pc4", "pc5", "pc6", "pc7n"], decl="const uint32_t ",
+                      bsel="CLT256V2_BSEL(%s, %s, %s)")
         em.emit("CLT256V2_S8_STAGE(z0, z1, z2, z3, z4, z5, z6, z7)")
         return em.lines, em.ops
     em.emit("const uint32_t inr = ~pc8 & ((~pc7 & pc6 & pc5) | (pc7 & ~pc6 & ~pc5));   // 96 <= popcount < 160")
@@ -145,7 +146,7 @@ def tail_lines(shape, kind="hist"):
         em.emit("const uint32_t %s = %s & inr;" % (nm, src))
         q.append(nm)
     # right shifts as multiply-high by a power of two held in a register: FMA pipe instead of the ALU pipe
-    gen_transpose(em, q, decl="const uint32_t ", shr="CLT256V2_SHR(%s, %d)")
+    gen_transpose(em, q, decl="const uint32_t ", shr="CLT256V2_SHR(%s, %d)", bsel="CLT256V2_BSEL(%s, %s, %s)")
     return em.lines, em.ops
 
 

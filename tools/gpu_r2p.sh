@@ -1,3 +1,6 @@
 set -x
-mkdir -p gpurun_out/r2u
-BLOCKS=148,140,136,132,128,124,120,112,104,96,128 WORDS_VARIANT=0 timeout 120 python tools/probe_words_blocks.py 2>&1 | tee gpurun_out/r2u/probe_words7_sweep2.txt
+mkdir -p gpurun_out/r2v
+timeout 900 python -m pytest tests/test_gpu_clt.py -x -q -m gpu 2>&1 | tail -3
+timeout 600 python bench.py --no-secondary > gpurun_out/r2v/bench_fused.json 2> gpurun_out/r2v/bench_fused.err; cut -c1-400 gpurun_out/r2v/bench_fused.json
+timeout 300 python tools/perf_probe.py streams 2>&1 | tee gpurun_out/r2v/streams.jsonl | cut -c1-200
+timeout 300 python bench.py --workload prbs_slicer > gpurun_out/r2v/bench_prbs_slicer.json 2>/dev/null; cut -c1-300 gpurun_out/r2v/bench_prbs_slicer.json
