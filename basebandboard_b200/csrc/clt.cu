@@ -18,6 +18,8 @@
 #include "bbb_internal.h"
 #include "clt_common.cuh"
 
+#include <mutex>
+
 // ---------------------------------------------------------------------------
 // seed kernel: planes[i*T + t] = bit i of the 32 streams of main-kernel thread t
 // ---------------------------------------------------------------------------
@@ -572,6 +574,49 @@ int bbb_clt_run_decimated(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64
 // ---------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------
+// ---------------------------------------------------------------------------
+// bbb_clt_hist_dev_static: bbb_clt_hist_dev for callers that must not allocate (CUDA graph capture of the work
+// around it, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// All device scratch of the call -- the bit-sliced start states, the jump-ahead
+// operators and the zeroed histogram the kernels accumulate into -- lives in ONE file-scope array that every GPU
+// loading the library holds until exit (4.51 MiB).  The data-driven kernel only (any loaded recurrence, n <= 512);
+// at most BBB_STATIC_MAX_STREAMS streams, so the clocks per stream grow with `count`.
+// The array is shared by every call on a device and keeps the last call's contents: the histogram part is cleared
+// per call, the rest is overwritten before use; calls that overlap on the GPU (two contexts or streams on one
+// device) race.
+// ---------------------------------------------------------------------------
+#define BBB_STATIC_MAX_T 2048u                                   /* threads of 32 streams */
+#define BBB_STATIC_MAX_STREAMS (BBB_STATIC_MAX_T * 32u)
+#define BBB_STATIC_MAX_NBITS 16u                                 /* stream index bits */
+#define BBB_STATIC_PLANE_WORDS ((size_t)BBB_MAX_N * BBB_STATIC_MAX_T)
+#define BBB_STATIC_JUMP_WORDS ((size_t)BBB_STATIC_MAX_NBITS * BBB_MAX_N * BBB_MAX_NW32)
+#define BBB_STATIC_HIST_WORDS ((size_t)2048)                     /* (n + 1) uint64 bins, n <= 512 */
+#define BBB_STATIC_WORDS (BBB_STATIC_PLANE_WORDS + BBB_STATIC_JUMP_WORDS + BBB_STATIC_HIST_WORDS)
+static_assert((BBB_MAX_N + 1) * 2 <= BBB_STATIC_HIST_WORDS, "histogram part too small");
+static_assert(BBB_STATIC_WORDS * 4 == BBB_STATIC_SCRATCH_BYTES, "include/bbb_b200.h states the size");
+static_assert(BBB_STATIC_PLANE_WORDS % 64 == 0 && BBB_STATIC_JUMP_WORDS % 64 == 0, "parts stay 256-byte aligned");
+
+static __device__ __align__(256) uint32_t bbb_static_scratch[BBB_STATIC_WORDS];
+
+// In host code the array's name is a stand-in, not a device address: the address is asked for once per device, with
+// that device current.
+static int static_scratch_ptr(bbb_ctx *c, uint32_t **out)
+{
+    static std::mutex mu;
+    static uint32_t *ptrs[64] = {};
+    if (c->device < 0 || c->device >= 64) return c->fail(BBB_EINVAL, "device index %d out of range", c->device);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptrs[c->device]) {
+        BBB_CUDA(c, cudaSetDevice(c->device));
+        void *p = nullptr;
+        BBB_CUDA(c, cudaGetSymbolAddress(&p, bbb_static_scratch));
+        if (!p) return c->fail(BBB_ECUDA, "cudaGetSymbolAddress returned null");
+        ptrs[c->device] = (uint32_t *)p;
+    }
+    *out = ptrs[c->device];
+    return BBB_OK;
+}
+
 static int check_loaded(bbb_ctx *c, const uint64_t *x0)
 {
     if (!c) return BBB_EINVAL;
@@ -602,6 +647,84 @@ int bbb_clt_hist_dev(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t co
                                                 (unsigned long long *)acc_dev);
     c->last_launches++;
     BBB_CUDA(c, cudaGetLastError());
+    c->end_call();
+    return BBB_OK;
+}
+
+int bbb_clt_hist_dev_static(bbb_ctx *c, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                            uint64_t *acc_dev)
+{
+    int rc = check_loaded(c, x0);
+    if (rc) return rc;
+    if (!acc_dev) return c->fail(BBB_EINVAL, "acc_dev is null");
+    if (model > 1) return c->fail(BBB_EINVAL, "bad model");
+    const uint32_t n = c->n, nw64 = (n + 63) / 64, nw32 = (n + 31) / 32;
+    if (n & (n - 1)) return c->fail(BBB_EINVAL, "CLTGRNG needs n a power of two (rng.py:73-74), n=%u", n);
+    if (count > (1ull << BBB_STATIC_MAX_LOG2_COUNT))
+        return c->fail(BBB_EINVAL, "bbb_clt_hist_dev_static: count %llu beyond the maximum 2^%u of the no-allocation variant "
+                                   "(static scratch of %zu bytes); use bbb_clt_hist_dev",
+                       (unsigned long long)count, BBB_STATIC_MAX_LOG2_COUNT, (size_t)BBB_STATIC_WORDS * 4);
+    BBB_CUDA(c, cudaSetDevice(c->device));
+    uint32_t *base = nullptr;
+    rc = static_scratch_ptr(c, &base);
+    if (rc) return rc;
+    uint32_t *const d_planes = base;
+    uint32_t *const d_jump = base + BBB_STATIC_PLANE_WORDS;
+    unsigned long long *const d_h = (unsigned long long *)(base + BBB_STATIC_PLANE_WORDS + BBB_STATIC_JUMP_WORDS);
+    c->begin_call();
+    BBB_CUDA(c, cudaMemsetAsync(d_h, 0, (n + 1) * sizeof(uint64_t), c->stream));   // the kernels ADD into it
+
+    uint64_t xl[BBB_MAX_NW64] = {0};
+    memcpy(xl, x0, nw64 * sizeof(uint64_t));
+    if (n % 64) xl[nw64 - 1] &= (1ull << (n % 64)) - 1;
+    advance_state(c, xl, first);
+    uint32_t Bg = 256;
+    while (Bg > 32 && (size_t)8 * n * Bg > 200 * 1024) Bg -= 32;
+    const size_t g_smem = (size_t)8 * n * Bg + (n + 1) * 4 + ((n + 2) & ~1u) * 2 + c->taps.size() * 2 + 16;
+    BBB_CUDA(c, cudaFuncSetAttribute(clt_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_smem));
+    const size_t per = (size_t)n * nw32;
+    std::vector<uint32_t> ops, one;      // host memory only
+
+    uint64_t done = 0;
+    while (done < count) {
+        // S <= 65536 streams of L = 2^logL clocks; the remainder goes round again with a shorter L
+        const uint64_t rem = count - done;
+        uint32_t logL = 0;
+        while ((rem >> logL) > BBB_STATIC_MAX_STREAMS) logL++;
+        const uint64_t S = rem >> logL;
+        const uint32_t T = (uint32_t)((S + 31) / 32);
+        uint32_t nbits = 0;
+        while (nbits < 40 && ((S - 1) >> nbits)) nbits++;
+        if (T > BBB_STATIC_MAX_T || nbits > BBB_STATIC_MAX_NBITS) return c->fail(BBB_EINVAL, "static geometry out of range");
+        if (nbits) {
+            ops.resize((size_t)nbits * per);
+            for (uint32_t b = 0; b < nbits; b++) {
+                c->pow2(logL + b).to_colmajor32(one);
+                memcpy(&ops[b * per], one.data(), per * 4);
+            }
+            // stream-ordered behind the previous round's kernels; `ops` is pageable: wait before it is rewritten
+            BBB_CUDA(c, c->h2d(d_jump, ops.data(), ops.size() * 4));
+            BBB_CUDA(c, cudaStreamSynchronize(c->stream));
+        }
+        SeedStart xs;
+        to_seed(xl, nw64, xs);
+        rc = launch_seed(c, d_jump, xs, nbits, T, d_planes);
+        if (rc) return rc;
+        GenericParams p;
+        p.n = n; p.nnz = (uint32_t)c->taps.size(); p.T = T; p.L = 1u << logL; p.model = model;
+        p.noise_var = 1; p.nw32out = 2 * nw64; p.nvalid = S; p.out_base = done;
+        p.row_ptr = c->d_row_ptr; p.taps = c->d_taps; p.planes = d_planes;
+        p.hist = d_h; p.out8 = nullptr; p.out16 = nullptr; p.out_words = nullptr; p.want_clt = 1u;
+        clt_generic_kernel<<<(T + Bg - 1) / Bg, Bg, g_smem, c->stream>>>(p);
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        advance_state(c, xl, S << logL);
+        done += S << logL;
+    }
+    fold_hist_kernel<<<1, 512, 0, c->stream>>>(d_h, n, (unsigned long long *)acc_dev);
+    c->last_launches++;
+    BBB_CUDA(c, cudaGetLastError());
+    c->last_kernel = "generic_static";
     c->end_call();
     return BBB_OK;
 }

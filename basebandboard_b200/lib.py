@@ -70,6 +70,7 @@ SIGNATURES = {
     "bbb_clt_hist": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, _u64p,
                                _P(C.c_int64), _u64p]),
     "bbb_clt_hist_dev": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p]),
+    "bbb_clt_hist_dev_static": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p]),
     "bbb_clt_stream": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32,
                                  _P(C.c_int8), _P(C.c_int16)]),
     "bbb_clt_stream_dev": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32,
@@ -277,6 +278,12 @@ class Context:
         x0 = state_words(init, self.n)
         self._check(self._L.bbb_clt_hist_dev(self._h, _ptr(x0, C.c_uint64), first, count, model,
                                              C.c_void_p(dev_ptr)))
+
+    def clt_hist_dev_static(self, init, first, count, model, dev_ptr):
+        """clt_hist_dev through the no-allocation entry point (static device scratch, count <= 2^32)."""
+        x0 = state_words(init, self.n)
+        self._check(self._L.bbb_clt_hist_dev_static(self._h, _ptr(x0, C.c_uint64), first, count, model,
+                                                    C.c_void_p(dev_ptr)))
 
     def clt_stream(self, init, first, count, model=MODEL_GATEWARE, noise_var=None, out=None):
         x0 = state_words(init, self.n)

@@ -134,6 +134,19 @@ int bbb_clt_hist(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t coun
  * ctx's stream (bbb_sync to wait). */
 int bbb_clt_hist_dev(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
                      uint64_t *acc_dev);
+/* bbb_clt_hist_dev without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture around the call, tight
+ * serving loops, harnesses that forbid it).  Same arguments, same result (ADDS into acc_dev, asynchronous
+ * on the ctx's stream), computed by the data-driven kernel for any loaded recurrence; it calls no
+ * cudaMalloc / cudaFree: its device scratch is one file-scope static array of BBB_STATIC_SCRATCH_BYTES
+ * that every GPU loading the library holds until exit.  Limits: count <= 2^BBB_STATIC_MAX_LOG2_COUNT
+ * samples per call (BBB_EINVAL beyond that, with a message naming the limit), n <= 512.  All calls on a
+ * device share the array: it keeps the last call's contents (the call clears what must start at zero),
+ * and calls that overlap on the GPU -- two contexts, or two host threads, on one device -- race. */
+#define BBB_STATIC_SCRATCH_BYTES 4726784u
+#define BBB_STATIC_MAX_LOG2_COUNT 32u
+int bbb_clt_hist_dev_static(bbb_ctx *ctx, const uint64_t *x0, uint64_t first, uint64_t count, uint32_t model,
+                            uint64_t *acc_dev);
 /* Materialised samples: out8[i] = g[first+i] as int8 (n <= 256), or
  * out16[i] = g[first+i] * noise_var as int16 (tx.py:75-76; noise_var = 1 gives
  * raw g).  Exactly one of out8/out16 is non-NULL. */
