@@ -486,6 +486,14 @@ clt256_s8v2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, 
 // through all spb samples, but only the sampled clock needs the CLT tree: that clock is the "s8" body
 // (popcount network, un-slice, slab), the other spb-1 are the clock alone ("plain" body: 492 LOP3, the
 // loads and stores of the non-resident planes).  Ld = decimated samples per stream (a multiple of 32).
+// CLT256_DEC_P2 (the default; 0 = the round-1 kernel): the plain clocks keep 161 planes in registers instead of 104 -- the popcount network's registers
+// are free there -- and the 57 extra ones are spilled to / filled from their shared-memory slots around the sampled
+// clock.  ncu on the 104-plane version: LSU data pipe 82 % busy, ALU pipe 74 %: the 152 LDS + 152 STS of every plain
+// clock were the limit.  (A compile-time switch and not a template parameter: cudafe++ of CUDA 12.9 does not finish on
+// the templated version of this kernel.)
+#ifndef CLT256_DEC_P2
+#define CLT256_DEC_P2 1
+#endif
 __global__ void __launch_bounds__(CLT256V2_B, CLT256V2_CTAS_PER_SM)
 clt256_dec_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t Ld, uint32_t spb, uint32_t delay,
                   int8_t *__restrict__ out, uint32_t *__restrict__ slab_base)
@@ -501,18 +509,40 @@ clt256_dec_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t Ld, 
 #include "clt256_v2_gen.inc"
 #undef CLT256V2_SECTION_RESIDENT_DECL
 
+#if CLT256_DEC_P2
+#define CLT256V2_SECTION_P2_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_P2_DECL
+#endif
+
 #pragma unroll 1
     for (uint32_t it = 0; it < Ld; it++) {
 #pragma unroll 1
         for (uint32_t ph = 0; ph < spb; ph++) {
             if (ph == delay) {
+#if CLT256_DEC_P2
+#define CLT256V2_SECTION_P2_SPILL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_P2_SPILL
+#endif
 #define CLT256V2_SECTION_S8_BODY
 #include "clt256_v2_gen.inc"
 #undef CLT256V2_SECTION_S8_BODY
+#if CLT256_DEC_P2
+#define CLT256V2_SECTION_P2_FILL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_P2_FILL
+#endif
             } else {
+#if CLT256_DEC_P2
+#define CLT256V2_SECTION_P2_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_P2_BODY
+#else
 #define CLT256V2_SECTION_P_BODY
 #include "clt256_v2_gen.inc"
 #undef CLT256V2_SECTION_P_BODY
+#endif
             }
         }
         if ((it & (CLT256V2_S8_K - 1u)) == 0u && it != 0u)
@@ -538,8 +568,9 @@ int bbb_clt_spec_dec_launch(bbb_ctx *c, uint32_t blocks, uint32_t Ld, uint32_t s
     const uint32_t T = blocks * CLT256V2_B;
     uint32_t *slab = (uint32_t *)c->scratch(11, (size_t)CLT256V2_S8_K * 8 * T * 4);
     if (!slab) return BBB_ECUDA;
-    BBB_CUDA(c, cudaFuncSetAttribute(clt256_dec_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2_STATE_BYTES));
-    clt256_dec_kernel<<<blocks, CLT256V2_B, CLT256V2_STATE_BYTES, c->stream>>>(planes, T, Ld, spb, delay, out, slab);
+    auto kern = clt256_dec_kernel;
+    BBB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V2_STATE_BYTES));
+    kern<<<blocks, CLT256V2_B, CLT256V2_STATE_BYTES, c->stream>>>(planes, T, Ld, spb, delay, out, slab);
     c->last_kernel = "clt256_dec";
     c->last_launches++;
     BBB_CUDA(c, cudaGetLastError());

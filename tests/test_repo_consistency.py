@@ -21,6 +21,15 @@ def test_generated_kernel_bodies_are_reproducible(tmp_path):
     assert "recurrence LOP3: 492, carry-save adders: 247, half adders: 8" in committed
 
 
+def test_generated_plain_clock_bodies_equal_the_recurrence():
+    """P_BODY (104 resident planes) and P2_BODY (161, with its spill / fill sections) of the committed .inc, run as
+    Python on random words, == five clocks of the shipped n256 recurrence (tools/check_clt256_bodies.py)."""
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "check_clt256_bodies.py")],
+                         capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stderr
+    assert res.stdout.startswith("ok")
+
+
 def test_bench_reference_arm_prints_the_contract_line():
     res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1",
                           "--warmup", "1", "--ref-step-seconds", "0.3", "--cpu-seconds", "0.5"],

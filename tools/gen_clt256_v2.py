@@ -29,6 +29,8 @@ ITERS = int(os.environ.get("CLT256V2_ITERS", "12000000"))
 SEED = int(os.environ.get("CLT256V2_SEED", "1"))
 NRES = int(os.environ.get("CLT256V2_RESIDENT", "104"))    # most planes kept in registers across clocks
 RES_BUDGET = int(os.environ.get("CLT256V2_RES_BUDGET", "200"))   # modelled live values allowed with them
+NRES_PLAIN = int(os.environ.get("CLT256V2_PLAIN_RESIDENT", "256"))   # resident planes of the plain-clock body P2
+PLAIN_BUDGET = int(os.environ.get("CLT256V2_PLAIN_BUDGET", "215"))
 # the committed load order (annealer output, 60M iterations, seed 3, lead 6; the settings here were picked
 # by a measured sweep on the B200, gpurun_out/variants.log); CLT256V2_REANNEAL=1 recomputes an order
 POS_FILE = None if os.environ.get("CLT256V2_REANNEAL") else \
@@ -47,7 +49,7 @@ def run_annealer(rows):
     return pos
 
 
-def pick_residents(rows, pos, nres, budget):
+def pick_residents(rows, pos, nres, budget, overlap=False, start=()):
     """Planes that stay in registers across the loop edge instead of going through shared memory.
     Plane b is finished at `done` and last needed in raw form at `death` of the next clock; it is
     eligible when done > death (the old value is dead before the new one exists) and costs one
@@ -66,12 +68,16 @@ def pick_residents(rows, pos, nres, budget):
         fold = ts[2] if len(ts) >= 3 else ts[-1]
         for t in ts[:3]:
             death[perm[t]] = max(death[perm[t]], fold)
-    cand = sorted(((N - times[b][-1]) + death[b], b) for b in range(N) if times[b][-1] > death[b])
+    # overlap: also planes whose new value exists before the old one is dead (two registers for a while; the body
+    # assigns those at the end of the clock).  start: planes that are resident in any case (their cost comes first).
+    cand = sorted(((N - times[b][-1]) + death[b], b) for b in range(N) if overlap or times[b][-1] > death[b])
+    cand = [(k, b) for k, b in cand if b in start] + [(k, b) for k, b in cand if b not in start]
     cur = clt256_sched.live_profile(rows, pos, LEAD).copy()
     chosen = set()
     for _, b in cand:
         if len(chosen) >= nres:
             break
+        budget_b = (1 << 30) if b in start else budget
         done = times[b][-1]
         add = np.zeros(N, dtype=np.int64)
         add[done:] += 1
@@ -79,9 +85,10 @@ def pick_residents(rows, pos, nres, budget):
         fr = pos[b] - LEAD
         if fr > done:
             add[done:fr] -= 1          # the wait for its slot is already in the profile
-        if (cur + add).max() <= budget:
+        if (cur + add).max() <= budget_b:
             cur += add
             chosen.add(b)
+    assert set(start) <= chosen
     return chosen
 
 
@@ -165,7 +172,7 @@ def carried_init(shape):
     return init
 
 
-def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
+def body_hist_v2(rows, pos, resident, shape=None, kind="hist", slot_resident=None):
     """shape None: dry run (returns the carried-plane shape); else the real body."""
     em = Emitter()
     perm = [0] * N
@@ -190,7 +197,10 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
     old_uses_left = {b: sum(1 for r in range(N) if b in rows[r]) for b in resident}
     assigned = set()
 
-    slot_of = slot_map(pos, resident)         # load time -> shared-memory slot (resident planes have none)
+    # load time -> shared-memory slot (resident planes have none; a body with MORE resident planes than the kernel's
+    # slot layout -- the plain clocks of the decimated stream -- passes the layout's set as slot_resident)
+    slot_of = slot_map(pos, resident if slot_resident is None else slot_resident)
+    deferred = []
 
     def wexpr(t):
         b = perm[t]
@@ -202,10 +212,19 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
         for tt, ex in store_at.pop(t, []):
             em.emit("st[%d * CLT256V2_B] = %s;" % (slot_of[tt], ex))
 
+    def used(exprs):
+        # the old value of a resident plane is read where the fold is emitted, not when its tap "arrives"
+        for ex in exprs:
+            if ex[0] == "r":
+                old_uses_left[int(ex[1:])] -= 1
+
     def finish(r, ex, t):
         if r in resident:
-            assert old_uses_left[r] == 0, "resident plane %d overwritten while its old value is needed" % r
-            em.emit("r%d = %s;" % (r, ex))
+            if old_uses_left[r] == 0:
+                em.emit("r%d = %s;" % (r, ex))
+            else:                             # the old value is still needed: the register changes hands at the end
+                em.emit("const uint32_t n%d = %s;" % (r, ex))
+                deferred.append(r)
             assigned.add(r)
             return
         slot = pos[r]
@@ -230,12 +249,11 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
         for r in taps_at[t]:
             pending[r].append(w)
             left[r] -= 1
-            if perm[t] in resident:
-                old_uses_left[perm[t]] -= 1
             if r not in acc and len(pending[r]) == 3:
                 nm = em.tmp()
                 em.emit("const uint32_t %s = %s ^ %s ^ %s;" % (nm, *pending[r]))
                 em.ops["rec"] += 1
+                used(pending[r])
                 pending[r] = []
                 if left[r] == 0:
                     finish(r, nm, t)
@@ -247,10 +265,13 @@ def body_hist_v2(rows, pos, resident, shape=None, kind="hist"):
                 nm = em.tmp()
                 em.emit("const uint32_t %s = %s;" % (nm, " ^ ".join(terms)))
                 em.ops["rec"] += 1
+                used(pending[r])
                 finish(r, nm, t)
     assert not store_at, store_at
     assert not tail
     assert assigned == set(resident)
+    for r in deferred:
+        em.emit("r%d = n%d;" % (r, r))
     if kind == "plain":
         # the clock alone (no popcount network, nothing emitted): the clocks between two sampled ones
         return em, perm
@@ -292,6 +313,10 @@ def main():
     emw, _ = body_hist_v2(rows, pos, resident, shape, "words")
     tail8, _ = tail_lines(shape, "s8")
     emp, _ = body_hist_v2(rows, pos, resident, shape, "plain")
+    # the plain clocks of the decimated stream with MORE resident planes (the popcount network's registers are free
+    # there): same slot layout; the extra planes are spilled to / filled from their slots around a sampled clock
+    res_p = pick_residents(rows, pos, NRES_PLAIN, PLAIN_BUDGET, overlap=True, start=resident)
+    emp2, _ = body_hist_v2(rows, pos, res_p, shape, "plain", slot_resident=resident)
     # CLT256V2_OUT / CLT256V2_PREFIX: a second instance with its own settings and macro prefix (the decimated-stream
     # kernel's bodies, clt256_dec_gen.inc, are generated with more resident planes: tools/gen_clt256_dec.sh)
     out = os.environ.get("CLT256V2_OUT") or os.path.join(ROOT, "basebandboard_b200", "csrc", "clt256_v2_gen.inc")
@@ -325,6 +350,18 @@ def main():
         f.write("\n".join(emw.lines))
         f.write("\n#endif\n#ifdef CLT256V2_SECTION_P_BODY\n// the clock alone: no popcount network, nothing emitted (decimated sample streams)\n")
         f.write("\n".join(emp.lines))
+        f.write("\n#endif\n#ifdef CLT256V2_SECTION_P2_DECL\n// %d more resident planes for the plain clocks (P2_BODY)\n" % (len(res_p) - len(resident)))
+        extra = sorted(res_p - resident)
+        for b in extra:
+            f.write("    uint32_t r%d = planes[(size_t)%d * T + t];\n" % (b, b))
+        f.write("#endif\n#ifdef CLT256V2_SECTION_P2_SPILL\n")
+        for b in extra:
+            f.write("    st[%d * CLT256V2_B] = r%d;\n" % (sm[pos[b]], b))
+        f.write("#endif\n#ifdef CLT256V2_SECTION_P2_FILL\n")
+        for b in extra:
+            f.write("    r%d = st[%d * CLT256V2_B];\n" % (b, sm[pos[b]]))
+        f.write("#endif\n#ifdef CLT256V2_SECTION_P2_BODY\n// the clock alone with %d resident planes\n" % len(res_p))
+        f.write("\n".join(emp2.lines))
         f.write("\n#endif\n")
     with open(real_out, "w") as g:
         g.write(f.getvalue().replace("CLT256V2_", prefix + "_"))
