@@ -486,8 +486,8 @@ clt256_s8v2_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, 
 // through all spb samples, but only the sampled clock needs the CLT tree: that clock is the "s8" body
 // (popcount network, un-slice, slab), the other spb-1 are the clock alone ("plain" body: 492 LOP3, the
 // loads and stores of the non-resident planes).  Ld = decimated samples per stream (a multiple of 32).
-// CLT256_DEC_P2 (the default; 0 = the round-1 kernel): the plain clocks keep 161 planes in registers instead of 104 -- the popcount network's registers
-// are free there -- and the 57 extra ones are spilled to / filled from their shared-memory slots around the sampled
+// CLT256_DEC_P2 (the default; 0 = the round-1 kernel): the plain clocks keep 151 planes in registers instead of 104 -- the popcount network's registers
+// are free there -- and the 47 extra ones are spilled to / filled from their shared-memory slots around the sampled
 // clock.  ncu on the 104-plane version: LSU data pipe 82 % busy, ALU pipe 74 %: the 152 LDS + 152 STS of every plain
 // clock were the limit.  (A compile-time switch and not a template parameter: cudafe++ of CUDA 12.9 does not finish on
 // the templated version of this kernel.)

@@ -22,7 +22,7 @@ def test_generated_kernel_bodies_are_reproducible(tmp_path):
 
 
 def test_generated_plain_clock_bodies_equal_the_recurrence():
-    """P_BODY (104 resident planes) and P2_BODY (161, with its spill / fill sections) of the committed .inc, run as
+    """P_BODY (104 resident planes) and P2_BODY (151, with its spill / fill sections) of the committed .inc, run as
     Python on random words, == five clocks of the shipped n256 recurrence (tools/check_clt256_bodies.py)."""
     res = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "check_clt256_bodies.py")],
                          capture_output=True, text=True, timeout=300)

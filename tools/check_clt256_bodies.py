@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Host-side check of the generated clock bodies (no GPU): evaluates the P_BODY (plain clock, 104 resident planes) and
-the P2_BODY (161 resident planes, with its DECL / SPILL / FILL sections) of clt256_v2_gen.inc as Python on random
+the P2_BODY (151 resident planes, with its DECL / SPILL / FILL sections) of clt256_v2_gen.inc as Python on random
 32-stream words and requires identical state after several clocks, in slots and registers, and against the
 recurrence itself (rng.py:38-40)."""
 import os
