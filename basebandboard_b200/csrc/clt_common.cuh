@@ -60,18 +60,25 @@ __device__ __forceinline__ uint32_t bit_select(uint32_t a, uint32_t b)
     return d;
 }
 
-template <int J, uint32_t M, int N>
+// x >> J as a multiply-high by 2^(32-J) read from constant memory: IMAD.HI on the FMA pipe instead of SHF on the ALU
+// pipe, which carries everything else of a transpose (the multiplier must not be a literal, or ptxas turns the
+// multiply back into the shift).  Index: J = 4, 2, 1 -> 0, 1, 2.
+static __constant__ uint32_t bbb_shr_mul[3] = {1u << 28, 1u << 30, 1u << 31};
+
+template <int J, uint32_t M, bool FMA_SHR, int N>
 __device__ __forceinline__ void transpose_bits_stage(uint32_t (&a)[N])
 {
+    const uint32_t mul = FMA_SHR ? bbb_shr_mul[J == 4 ? 0 : J == 2 ? 1 : 2] : 0u;
 #pragma unroll
     for (int k = 0; k < N; k++) {
         if (k & J) continue;
         const uint32_t x = a[k], y = a[k + J];
         a[k] = bit_select<M>(x, y << J);
-        a[k + J] = bit_select<M>(x >> J, y);
+        a[k + J] = bit_select<M>(FMA_SHR ? __umulhi(x, mul) : (x >> J), y);
     }
 }
 
+template <bool FMA_SHR = false>
 __device__ __forceinline__ void transpose32_fast(uint32_t (&a)[32])
 {
 #pragma unroll
@@ -87,9 +94,9 @@ __device__ __forceinline__ void transpose32_fast(uint32_t (&a)[32])
         a[k] = lo;
         a[k + 8] = hi;
     }
-    transpose_bits_stage<4, 0x0F0F0F0Fu>(a);
-    transpose_bits_stage<2, 0x33333333u>(a);
-    transpose_bits_stage<1, 0x55555555u>(a);
+    transpose_bits_stage<4, 0x0F0F0F0Fu, FMA_SHR>(a);
+    transpose_bits_stage<2, 0x33333333u, FMA_SHR>(a);
+    transpose_bits_stage<1, 0x55555555u, FMA_SHR>(a);
 }
 
 // acc[0..n] += hist[0..n]; acc[n+1] += sum g*h; acc[n+2] += sum g^2*h with g = bin - n/2.

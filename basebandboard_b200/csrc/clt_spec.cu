@@ -1103,10 +1103,26 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8])
 
 #pragma push_macro("CLT256V2_W_DRAIN")
 #pragma push_macro("CLT256V2_W_BEGIN")
+#pragma push_macro("CLT256V2_W_EMIT")
 #pragma push_macro("CLT256V2_W_END")
 #undef CLT256V2_W_DRAIN
 #undef CLT256V2_W_BEGIN
+#undef CLT256V2_W_EMIT
 #undef CLT256V2_W_END
+// W7_STRAIGHT: the eight words of a clock as straight-line code (the cases fall through, each with its own transpose
+// and tcgen05.st) instead of a loop over a switch that first copies the 32 source planes of the word into tw[]
+#define CLT256V2_W_EMIT(w, r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16, r17, r18, r19, \
+                        r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31)                                  \
+        case w: {                                                                                                    \
+            const uint32_t src[32] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15, r16,     \
+                                      r17, r18, r19, r20, r21, r22, r23, r24, r25, r26, r27, r28, r29, r30, r31};    \
+            _Pragma("unroll") for (int i = 0; i < 32; i++) tw[i] = src[i];                                           \
+            if (W7_STRAIGHT) {                                                                                       \
+                transpose32_fast(tw);                                                                                \
+                tmem_st32(taddr + b_ * 256u + (w) * 32u, tw);                                                        \
+            }                                                                                                        \
+        }                                                                                                            \
+        if (!W7_STRAIGHT) break;
 #define CLT256V2_W_DRAIN(j)
 #define CLT256V2_W_BEGIN                                                                                             \
     const uint32_t b_ = it & 1u, k_ = it >> 1;                                                                       \
@@ -1114,13 +1130,15 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8])
         mbar_wait(bar_empty + 8u * b_, (k_ - 1u) & 1u);                                                              \
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");                                              \
     }                                                                                                                \
-    _Pragma("unroll 1") for (uint32_t w_ = 0; w_ < 8u; w_++) {                                                       \
+    _Pragma("unroll 1") for (uint32_t w_ = 0; w_ < (W7_STRAIGHT ? 1u : 8u); w_++) {                                  \
         uint32_t tw[32];                                                                                             \
-        switch (w_) {
+        switch (W7_STRAIGHT ? 0u : w_) {
 #define CLT256V2_W_END                                                                                               \
         }                                                                                                            \
-        if (!W7_SPLIT || w_ < 4u) transpose32_fast(tw);   /* SPLIT: words 4-7 go to TMEM bit-sliced */                 \
-        tmem_st32(taddr + b_ * 256u + w_ * 32u, tw);                                                                 \
+        if (!W7_STRAIGHT) {                                                                                          \
+            if (!W7_SPLIT || w_ < 4u) transpose32_fast<W7_FMA_SHR>(tw);   /* SPLIT: words 4-7 go to TMEM bit-sliced */ \
+            tmem_st32(taddr + b_ * 256u + w_ * 32u, tw);                                                             \
+        }                                                                                                            \
     }                                                                                                                \
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");                                                     \
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");                                                 \
@@ -1134,7 +1152,9 @@ template <int POLICY2, int SPLIT>
 __global__ void __launch_bounds__(2 * CLT256V2_B, 1)
 clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
 {
-    constexpr bool W7_SPLIT = SPLIT != 0;
+    constexpr bool W7_SPLIT = SPLIT == 1;
+    constexpr bool W7_STRAIGHT = SPLIT == 3;      // knob words_variant = 12
+    constexpr bool W7_FMA_SHR = SPLIT == 2;       // knob words_variant = 11: right shifts of the transposes on the FMA pipe
     extern __shared__ uint4 smem4[];
     const uint32_t ctrl = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
     const uint32_t warp = threadIdx.x >> 5, pair = warp & 3u, lane = threadIdx.x & 31u;
@@ -1247,6 +1267,7 @@ clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
     if (warp == 4u) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
 }
 #pragma pop_macro("CLT256V2_W_END")
+#pragma pop_macro("CLT256V2_W_EMIT")
 #pragma pop_macro("CLT256V2_W_BEGIN")
 #pragma pop_macro("CLT256V2_W_DRAIN")
 
@@ -1510,7 +1531,9 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         c->last_kernel = "clt256_words3";
     } else if (c->tune_spec_variant != 1 && c->tune_words_variant != 2) {
         auto kern = c->tune_words_variant == 8 ? clt256_words7_kernel<0, 0>
-                    : c->tune_words_variant == 10 ? clt256_words7_kernel<1, 1> : clt256_words7_kernel<1, 0>;
+                    : c->tune_words_variant == 10 ? clt256_words7_kernel<1, 1>
+                    : c->tune_words_variant == 11 ? clt256_words7_kernel<1, 2>
+                    : c->tune_words_variant == 12 ? clt256_words7_kernel<1, 3> : clt256_words7_kernel<1, 0>;
         BBB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V7_SMEM));
         kern<<<blocks, 2 * CLT256V2_B, CLT256V7_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
         c->last_kernel = "clt256_words7";

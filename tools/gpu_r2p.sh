@@ -1,5 +1,4 @@
 set -x
-mkdir -p gpurun_out/r2x
-timeout 900 python -m pytest tests/test_gpu_clt.py tests/test_gpu_prbs.py tests/test_shaper.py -x -q -m gpu 2>&1 | tail -3
-for w in prbs_slicer prbs_shaped_slicer; do timeout 300 python bench.py --workload $w > gpurun_out/r2x/bench_$w.json 2>/dev/null; cut -c1-130 gpurun_out/r2x/bench_$w.json; python -c "
-import json; d=json.load(open('gpurun_out/r2x/bench_$w.json')); print(d['value'], d.get('roofline',{}).get('frac'), d['e2e']['value'])"; done
+mkdir -p gpurun_out/r2y
+timeout 300 python -m pytest tests/test_gpu_clt.py -x -q -m gpu -k "word_stream" 2>&1 | tail -3
+for v in 12 0 12 0; do BLOCKS=37,0 WORDS_VARIANT=$v timeout 120 python tools/probe_words_blocks.py 2>&1 | tee -a gpurun_out/r2y/probe_words7_straight.txt; done
