@@ -333,6 +333,7 @@ int bbb_set_tuning(bbb_ctx *c, const char *key, int64_t value)
     else if (!strcmp(key, "clt_spec_max_blocks")) c->tune_spec_max_blocks = value < 0 ? 0u : (uint32_t)value;
     else if (!strcmp(key, "words_variant")) c->tune_words_variant = (int)value;
     else if (!strcmp(key, "words_b192")) c->tune_words_b192 = value != 0;
+    else if (!strcmp(key, "seed_single")) c->tune_seed_single = value != 0;
     else if (!strcmp(key, "dec_full_stream")) c->tune_dec_full_stream = value != 0;
     else if (!strcmp(key, "slicer_chunk_bits")) c->tune_slicer_chunk_bits = value < 64 ? 0ull : ((uint64_t)value & ~63ull);
     else if (!strcmp(key, "prbs_chunk_words")) c->tune_prbs_chunk_words = value < 0 ? 0u : (uint32_t)value;

@@ -61,6 +61,7 @@ struct bbb_ctx {
     uint64_t tune_slicer_chunk_bits = 0; // 0: 2^27 PRBS bits per pass of the slicer-loop composite
     int tune_words_variant = 0;         // raw-word kernel: 0 default, 2 clt256_words2_kernel, 4 clt256_words4_kernel (two CTAs per SM)
     int tune_words_b192 = 0;            // 1: raw-word stream on the 192-thread experiment (clt256_words3_kernel)
+    int tune_seed_single = 0;           // 1: always the one-group-per-warp seeding kernel
     int tune_dec_full_stream = 0;       // 1: decimated samples by the full stream + pick (never clt256_dec_kernel)
     int nest = 0;                       // > 0 inside a composite ABI call (begin_call/end_call are the outer call's)
     uint32_t tune_prbs_chunk_words = 0; // 0: automatic detector chunk length (64-bit words)

@@ -92,6 +92,104 @@ seed_kernel(const uint32_t *__restrict__ J,   // [nbits][n][NW32] column-major j
     }
 }
 
+// Four stream groups per warp.  ncu on seed_kernel<8> at 2^19 streams (0.28 ms, 9 % of an 8 GiB word-stream call): the
+// L1 data pipe is 90 % busy -- every application of an operator reads all of it (8 KB for n = 256) for ONE state.
+// Here a warp carries the states of four consecutive stream groups and a column of the operator, once loaded, is
+// folded into all four (mask instead of predicate: acc ^= column & m_v), so the operator traffic per state drops to a
+// quarter.  Same arithmetic, same results; used for n = 97..128 and 225..256 (four or eight state words) when there are enough groups to fill the GPU.
+template <int NW32>
+__global__ void __launch_bounds__(128, 4)
+seed4_kernel(const uint32_t *__restrict__ J, SeedStart xs, uint32_t n, uint32_t nbits, uint32_t T,
+             uint32_t *__restrict__ planes)
+{
+    constexpr int V = 4;
+    static_assert(NW32 % 4 == 0 && NW32 <= 8, "128-bit operator loads; three sets of V * NW32 words stay in registers");
+    const uint32_t gw0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * V;   // first main-kernel thread of this warp
+    const uint32_t lane = threadIdx.x & 31;
+    if (gw0 >= T) return;
+    // lane l keeps the states after l applications of A^L: parked in shared memory (column = lane), not in 32 registers
+    __shared__ uint32_t park[4][V][NW32][32];
+    uint32_t (*const xp)[NW32][32] = park[threadIdx.x >> 5];
+    uint32_t y[V][NW32];
+#pragma unroll
+    for (int v = 0; v < V; v++)
+#pragma unroll
+        for (int w = 0; w < NW32; w++) y[v][w] = xs.w[w];
+    auto apply = [&](const uint32_t *Jb, uint32_t vmask) {
+        uint32_t acc[V][NW32];
+#pragma unroll
+        for (int v = 0; v < V; v++)
+#pragma unroll
+            for (int w = 0; w < NW32; w++) acc[v][w] = 0;
+#pragma unroll
+        for (int k = 0; k < NW32; k++) {
+            const uint32_t col = (uint32_t)k * 32u + lane;
+            if (col < n) {
+                uint32_t m[V];
+#pragma unroll
+                for (int v = 0; v < V; v++) m[v] = 0u - ((y[v][k] >> lane) & (vmask >> v) & 1u);
+                const uint32_t *cp = Jb + (size_t)col * NW32;
+#pragma unroll
+                for (int w = 0; w < NW32; w += 4) {
+                    const uint4 c4 = __ldg((const uint4 *)(cp + w));
+#pragma unroll
+                    for (int v = 0; v < V; v++) {
+                        acc[v][w] ^= c4.x & m[v]; acc[v][w + 1] ^= c4.y & m[v];
+                        acc[v][w + 2] ^= c4.z & m[v]; acc[v][w + 3] ^= c4.w & m[v];
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int v = 0; v < V; v++)
+            if ((vmask >> v) & 1u) {                      // warp-uniform
+#pragma unroll
+                for (int w = 0; w < NW32; w++) y[v][w] = __reduce_xor_sync(0xffffffffu, acc[v][w]);
+            }
+    };
+    for (uint32_t b = 5; b < nbits; b++) {
+        uint32_t vmask = 0;
+#pragma unroll
+        for (int v = 0; v < V; v++) vmask |= (((gw0 + v) >> (b - 5)) & 1u) << v;
+        if (vmask) apply(J + (size_t)b * n * NW32, vmask);
+    }
+#pragma unroll
+    for (int v = 0; v < V; v++)
+#pragma unroll
+        for (int w = 0; w < NW32; w++) xp[v][w][lane] = y[v][w];      // nbits == 0: every lane the start state
+    if (nbits > 0) {
+#pragma unroll 1
+        for (uint32_t l = 1; l < 32; l++) {
+            apply(J, (1u << V) - 1u);
+            if (lane == l) {
+#pragma unroll
+                for (int v = 0; v < V; v++)
+#pragma unroll
+                    for (int w = 0; w < NW32; w++) xp[v][w][lane] = y[v][w];
+            }
+        }
+    }
+    __syncwarp();
+    // ballot transpose: word i of thread gw = bit i of every lane's state
+#pragma unroll
+    for (int v = 0; v < V; v++) {
+        const uint32_t gw = gw0 + v;
+        if (gw >= T) break;                               // warp-uniform
+#pragma unroll
+        for (int w = 0; w < NW32; w++) {
+            uint32_t keep = 0;
+            const uint32_t xw = xp[v][w][lane];
+#pragma unroll
+            for (int k = 0; k < 32; k++) {
+                const uint32_t bal = __ballot_sync(0xffffffffu, (xw >> k) & 1u);
+                if (lane == (uint32_t)k) keep = bal;
+            }
+            const uint32_t i = (uint32_t)w * 32u + lane;
+            if (i < n) planes[(size_t)i * T + gw] = keep;
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------
 // generic main kernel: any recurrence, taps read from shared memory
 // ---------------------------------------------------------------------------
@@ -240,6 +338,14 @@ static int launch_seed(bbb_ctx *c, const uint32_t *dJ, const SeedStart &xs, uint
 {
     const uint32_t n = c->n, nw32 = (n + 31) / 32;
     const uint32_t threads = 256;
+    if ((nw32 == 4 || nw32 == 8) && T >= 8u * (uint32_t)c->sm_count && !c->tune_seed_single) {
+        const uint32_t warps = (T + 3) / 4, blocks4 = (warps + 3) / 4;       // 128-thread blocks
+        if (nw32 == 4) seed4_kernel<4><<<blocks4, 128, 0, c->stream>>>(dJ, xs, n, nbits, T, d_planes);
+        else seed4_kernel<8><<<blocks4, 128, 0, c->stream>>>(dJ, xs, n, nbits, T, d_planes);
+        c->last_launches++;
+        BBB_CUDA(c, cudaGetLastError());
+        return BBB_OK;
+    }
     const uint32_t blocks = (uint32_t)(((uint64_t)T * 32 + threads - 1) / threads);
 #define SEED_CASE(NW) \
     case NW: seed_kernel<NW><<<blocks, threads, 0, c->stream>>>(dJ, xs, n, nbits, T, d_planes); break

@@ -349,6 +349,32 @@ def test_spec256_streams_equal_generic_large(ctx):
     assert bool(torch.equal(wa, wb))
 
 
+@pytest.mark.parametrize("n", [128, 256])
+def test_four_group_seeding_equals_single_group_seeding(ctx, n):
+    """seed4_kernel (four stream groups per warp, used from 8 groups per SM up) == seed_kernel, through the word
+    stream of launches big enough to take it (data-driven kernel for n = 128, both kernels for n = 256)."""
+    import torch
+    ctx.lutopt_load_shipped(n)
+    count = (1 << 23) + 4099
+    words = n // 64
+    a = torch.empty(count * words, dtype=torch.int64, device="cuda")
+    b = torch.empty(count * words, dtype=torch.int64, device="cuda")
+    try:
+        for no_spec in ((0, 1) if n == 256 else (0,)):
+            ctx.set_tuning("clt_no_spec", no_spec)
+            ctx.set_tuning("seed_single", 0)
+            ctx.lutopt_stream_dev(1, (1 << 37) + 3, count, a.data_ptr())
+            ctx.sync()
+            ctx.set_tuning("seed_single", 1)
+            ctx.lutopt_stream_dev(1, (1 << 37) + 3, count, b.data_ptr())
+            ctx.sync()
+            assert bool(torch.equal(a, b)), (n, no_spec)
+    finally:
+        ctx.set_tuning("seed_single", 0)
+        ctx.set_tuning("clt_no_spec", 0)
+        ctx.lutopt_load_shipped(256)
+
+
 @pytest.mark.parametrize("variant", [1, 2])
 @pytest.mark.parametrize("noise_var", [0, 1, 8, 15])
 def test_spec256_int16_noise_stream_matches_oracle(ctx, orc, noise_var, variant):
