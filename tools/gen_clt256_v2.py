@@ -6,7 +6,7 @@ clock + CLTGRNG popcount network + histogram indices on 32 bit-sliced streams pe
 Differences from tools/gen_clt256.py (two passes, 128 fixed accumulators, 768 shared-memory words
 per clock): the old state is read ONCE (256 words) in the load order tools/clt256_anneal.c chose,
 rows are folded as their taps arrive (3 taps -> one LOP3, the 4th -> a second one: 492 LOP3, the
-minimum), new planes are stored IN PLACE as soon as their slot has been read (256 words), and
+minimum without sub-sums shared between rows), new planes are stored IN PLACE as soon as their slot has been read (256 words), and
 planes that finish late and are needed early in the next clock may stay in registers across the
 loop edge ("resident" planes: no store, no load).
 
