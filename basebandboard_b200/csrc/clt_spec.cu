@@ -1402,6 +1402,154 @@ clt256_words8_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #pragma pop_macro("CLT256V2_W_DRAIN")
 
 // ---------------------------------------------------------------------------
+// clt256_words9_kernel (knob words_variant = 13): words7 with THREE clocks of staging -- the two tensor-memory
+// buffers and the 128 KB shared-memory stage of words2 -- so that the drain warps take the clocks in PAIRS: the two
+// sectors a stream gets from clocks 2k, 2k+1 are adjacent (64 bytes of one 128-byte line) and leave back to back.
+// tools/probe_store_pattern.cu: 606 k streams take 2575 GB/s in 32-byte visits and 4041 GB/s in 64-byte visits.
+// Clock `it` goes to buffer it % 3 (0, 1: TMEM columns 0 / 256; 2: shared memory, word [stream][word][thread]); pair k
+// = buffers (2k % 3, (2k + 1) % 3) is drained while clock 2k + 2 is computed, clock 2k + 3 re-uses the first of them.
+// ---------------------------------------------------------------------------
+#define CLT256V9_STAGE_BYTES (32 * 8 * CLT256V2_B * 4)
+#define CLT256V9_SMEM (CLT256V2_STATE_BYTES + CLT256V9_STAGE_BYTES + CLT256V7_CTRL_BYTES)
+
+#pragma push_macro("CLT256V2_W_DRAIN")
+#pragma push_macro("CLT256V2_W_BEGIN")
+#pragma push_macro("CLT256V2_W_END")
+#undef CLT256V2_W_DRAIN
+#undef CLT256V2_W_BEGIN
+#undef CLT256V2_W_END
+#define CLT256V2_W_DRAIN(j)
+#define CLT256V2_W_BEGIN                                                                                             \
+    const uint32_t b_ = it % 3u, u_ = it / 3u;                                                                       \
+    if (u_ != 0u) {                      /* the drain warp has read use u_-1 of this buffer */                        \
+        mbar_wait(bar_empty + 8u * b_, (u_ - 1u) & 1u);                                                              \
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");                                              \
+    }                                                                                                                \
+    _Pragma("unroll 1") for (uint32_t w_ = 0; w_ < 8u; w_++) {                                                       \
+        uint32_t tw[32];                                                                                             \
+        switch (w_) {
+#define CLT256V2_W_END                                                                                               \
+        }                                                                                                            \
+        transpose32_fast(tw);                                                                                        \
+        if (b_ < 2u) {                                                                                               \
+            tmem_st32(taddr + b_ * 256u + w_ * 32u, tw);                                                             \
+        } else {                                                                                                     \
+            const uint32_t sa = stage_t + w_ * (uint32_t)(CLT256V2_B * 4);                                           \
+            _Pragma("unroll") for (int j = 0; j < 32; j++)                                                           \
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(sa + (uint32_t)(j * 8 * CLT256V2_B * 4)), "r"(tw[j]) : "memory"); \
+        }                                                                                                            \
+    }                                                                                                                \
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");                                                     \
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");                                                 \
+    mbar_arrive(bar_full + 8u * b_);                     /* release: the shared-memory stores are visible too */
+
+// eight streams x eight words of one staged clock: from tensor memory (buf 0, 1) or the shared-memory stage (buf 2)
+__device__ __forceinline__ void w9_load(uint32_t buf, uint32_t taddr, uint32_t stage_t, uint32_t jb, uint32_t (&v)[8][8])
+{
+    if (buf < 2u) {
+#pragma unroll
+        for (uint32_t w = 0; w < 8u; w++) tmem_ld8(taddr + buf * 256u + w * 32u + jb, v[w]);
+    } else {
+#pragma unroll
+        for (uint32_t w = 0; w < 8u; w++)
+#pragma unroll
+            for (uint32_t jj = 0; jj < 8u; jj++)
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[w][jj])
+                             : "r"(stage_t + (uint32_t)((((jb + jj) * 8u + w) * CLT256V2_B) * 4u)) : "memory");
+    }
+}
+
+// the lane pair's two 16-byte stores of one stream's 32-byte clock (see clt256_words7_kernel)
+__device__ __forceinline__ void w9_store(const uint32_t (&v)[8][8], uint32_t jj, uint32_t odd, uint32_t *pa, uint32_t *pb,
+                                         uint64_t pol)
+{
+    uint32_t keep[4], got[4];
+#pragma unroll
+    for (uint32_t i = 0; i < 4u; i++) {
+        keep[i] = odd ? v[4 + i][jj] : v[i][jj];
+        got[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i][jj] : v[4 + i][jj], 1);
+    }
+    st_policy((uint4 *)pa, odd ? make_uint4(got[0], got[1], got[2], got[3]) : make_uint4(keep[0], keep[1], keep[2], keep[3]), pol);
+    st_policy((uint4 *)pb, odd ? make_uint4(keep[0], keep[1], keep[2], keep[3]) : make_uint4(got[0], got[1], got[2], got[3]), pol);
+}
+
+__global__ void __launch_bounds__(2 * CLT256V2_B, 1)
+clt256_words9_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
+{
+    extern __shared__ uint4 smem4[];
+    const uint32_t stage_base = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
+    const uint32_t ctrl = stage_base + CLT256V9_STAGE_BYTES;
+    const uint32_t warp = threadIdx.x >> 5, pair = warp & 3u, lane = threadIdx.x & 31u;
+    if (warp == 4u) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(ctrl + 192u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (threadIdx.x == 0)
+        for (uint32_t i = 0; i < 24u; i++) mbar_init(ctrl + 8u * i, 32u);     // [warp pair][full 0-2, empty 0-2]
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tbase = *(const volatile uint32_t *)((const char *)smem4 + CLT256V2_STATE_BYTES + CLT256V9_STAGE_BYTES + 192);
+    const uint32_t taddr = tbase + ((pair * 32u) << 16);
+    const uint32_t bar_full = ctrl + pair * 48u, bar_empty = bar_full + 24u;
+    const uint32_t stage_t = stage_base + (pair * 32u + lane) * 4u;            // this thread's column of the stage
+    if (warp >= 4u) {
+        const uint32_t odd = lane & 1u;
+        uint32_t *const opa = out + (size_t)(blockIdx.x * CLT256V2_B + pair * 32u + (lane & ~1u)) * 32u * L * 8u + 4u * odd;
+        uint32_t *const opb = opa + (size_t)32u * L * 8u;
+        uint64_t pol_keep, pol_done;
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_done));
+#pragma unroll 1
+        for (uint32_t it = 0; it < L; it += 2u) {
+            const bool two = it + 1u < L;
+            const uint32_t ba = it % 3u, bb = (it + 1u) % 3u;
+            mbar_wait(bar_full + 8u * ba, (it / 3u) & 1u);
+            if (two) mbar_wait(bar_full + 8u * bb, ((it + 1u) / 3u) & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+            for (uint32_t jb = 0; jb < 32u; jb += 8u) {
+                uint32_t va[8][8], vb[8][8];
+                w9_load(ba, taddr, stage_t, jb, va);
+                if (two) w9_load(bb, taddr, stage_t, jb, vb);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (uint32_t jj = 0; jj < 8u; jj++) {
+                    const uint32_t sec = (jb + jj) * L + it;
+                    const size_t off = (size_t)sec * 8u;
+                    w9_store(va, jj, odd, opa + off, opb + off, (sec & 3u) == 3u ? pol_done : pol_keep);
+                    if (two) w9_store(vb, jj, odd, opa + off + 8, opb + off + 8, ((sec + 1u) & 3u) == 3u ? pol_done : pol_keep);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(bar_empty + 8u * ba);
+            if (two) mbar_arrive(bar_empty + 8u * bb);
+        }
+    } else {
+        const uint32_t tid = threadIdx.x;
+        const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+        uint32_t *const st = (uint32_t *)smem4 + tid;
+        for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+        for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_W_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_W_BODY
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 4u) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
+}
+#pragma pop_macro("CLT256V2_W_END")
+#pragma pop_macro("CLT256V2_W_BEGIN")
+#pragma pop_macro("CLT256V2_W_DRAIN")
+
+// ---------------------------------------------------------------------------
 // clt256_words3_kernel (EXPERIMENT, knob "words_b192"; measured and rejected): the same clock and transposes with
 // SIX warps per SM instead of four.  ncu on words2 shows neither pipe busy (ALU 34 %, LSU 36 %), so more warps
 // looked like the fix; but 192 threads need 114 KB of state, which leaves room for only HALF a clock of staging
@@ -1504,6 +1652,11 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
                                                                              (int32_t)noise_var);
         c->last_kernel = "clt256_s16";
+    } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 13) {
+        static_assert(CLT256V9_SMEM <= 227 * 1024, "shared memory budget");
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_words9_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V9_SMEM));
+        clt256_words9_kernel<<<blocks, 2 * CLT256V2_B, CLT256V9_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
+        c->last_kernel = "clt256_words9";
     } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 9) {
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V7_SMEM));
         clt256_words8_kernel<<<blocks, 2 * CLT256V2_B, CLT256V7_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
