@@ -99,6 +99,25 @@ __device__ __forceinline__ void transpose32_fast(uint32_t (&a)[32])
     transpose_bits_stage<1, 0x55555555u, FMA_SHR>(a);
 }
 
+// The 32x32 transpose in two halves that commute: the three sub-byte stages on all 32 rows (here), and the two
+// byte-granular stages, which only mix rows k, k+8, k+16, k+24 (byte4x4_transpose on those four).
+__device__ __forceinline__ void transpose32_bit_stages(uint32_t (&a)[32])
+{
+    transpose_bits_stage<4, 0x0F0F0F0Fu, false>(a);
+    transpose_bits_stage<2, 0x33333333u, false>(a);
+    transpose_bits_stage<1, 0x55555555u, false>(a);
+}
+
+__device__ __forceinline__ void byte4x4_transpose(uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3)
+{
+    const uint32_t lo02 = __byte_perm(r0, r2, 0x5410), hi02 = __byte_perm(r0, r2, 0x7632);
+    const uint32_t lo13 = __byte_perm(r1, r3, 0x5410), hi13 = __byte_perm(r1, r3, 0x7632);
+    r0 = __byte_perm(lo02, lo13, 0x6240);
+    r1 = __byte_perm(lo02, lo13, 0x7351);
+    r2 = __byte_perm(hi02, hi13, 0x6240);
+    r3 = __byte_perm(hi02, hi13, 0x7351);
+}
+
 // acc[0..n] += hist[0..n]; acc[n+1] += sum g*h; acc[n+2] += sum g^2*h with g = bin - n/2.
 // Exact integer arithmetic: the moments of the sample set are functions of its histogram.
 static __global__ void fold_hist_kernel(const unsigned long long *__restrict__ hist, uint32_t n,

@@ -1135,7 +1135,12 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8])
         switch (W7_STRAIGHT ? 0u : w_) {
 #define CLT256V2_W_END                                                                                               \
         }                                                                                                            \
-        if (!W7_STRAIGHT) {                                                                                          \
+        if (W7_BYTES) {      /* sub-byte stages here; column 4*jl + c holds row jl + 8c for the drain's byte stages */ \
+            transpose32_bit_stages(tw);                                                                              \
+            uint32_t tp[32];                                                                                         \
+            _Pragma("unroll") for (int cc = 0; cc < 32; cc++) tp[cc] = tw[(cc >> 2) + 8 * (cc & 3)];                 \
+            tmem_st32(taddr + b_ * 256u + w_ * 32u, tp);                                                             \
+        } else if (!W7_STRAIGHT) {                                                                                   \
             if (!W7_SPLIT || w_ < 4u) transpose32_fast<W7_FMA_SHR>(tw);   /* SPLIT: words 4-7 go to TMEM bit-sliced */ \
             tmem_st32(taddr + b_ * 256u + w_ * 32u, tw);                                                             \
         }                                                                                                            \
@@ -1154,6 +1159,7 @@ clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 {
     constexpr bool W7_SPLIT = SPLIT == 1;
     constexpr bool W7_STRAIGHT = SPLIT == 3;      // knob words_variant = 12
+    constexpr bool W7_BYTES = SPLIT == 4;         // the byte-granular transpose stages run on the drain warps
     constexpr bool W7_FMA_SHR = SPLIT == 2;       // knob words_variant = 11: right shifts of the transposes on the FMA pipe
     extern __shared__ uint4 smem4[];
     const uint32_t ctrl = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
@@ -1225,6 +1231,13 @@ clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 #pragma unroll
                 for (uint32_t w = 0; w < 8u; w++) tmem_ld8(taddr + b * 256u + w * 32u + jb, v[w]);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (W7_BYTES) {
+#pragma unroll
+                    for (uint32_t w = 0; w < 8u; w++) {
+                        byte4x4_transpose(v[w][0], v[w][1], v[w][2], v[w][3]);
+                        byte4x4_transpose(v[w][4], v[w][5], v[w][6], v[w][7]);
+                    }
+                }
 #pragma unroll
                 for (uint32_t jj = 0; jj < 8u; jj++) {
                         uint32_t keep[4], got[4];
@@ -1233,7 +1246,9 @@ clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
                             keep[i] = odd ? v[4 + i][jj] : v[i][jj];
                             got[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i][jj] : v[4 + i][jj], 1);
                         }
-                        const uint32_t sec = (jb + jj) * L + it;          // sector number within the thread's 32 streams
+                        // BYTES: this batch holds streams 2m + {0, 1} + 8c, m = jb / 8
+                        const uint32_t sj = W7_BYTES ? (jb >> 2) + (jj >> 2) + 8u * (jj & 3u) : jb + jj;
+                        const uint32_t sec = sj * L + it;                 // sector number within the thread's 32 streams
                         const size_t off = (size_t)sec * 8u;
                         // (releasing HALF lines -- evict_first on every odd sector -- measured 2497 against 2834 GB/s)
                         const uint64_t pol = POLICY2 && (sec & 3u) == 3u ? pol_done : pol_keep;
@@ -1687,7 +1702,8 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         auto kern = c->tune_words_variant == 8 ? clt256_words7_kernel<0, 0>
                     : c->tune_words_variant == 10 ? clt256_words7_kernel<1, 1>
                     : c->tune_words_variant == 11 ? clt256_words7_kernel<1, 2>
-                    : c->tune_words_variant == 12 ? clt256_words7_kernel<1, 3> : clt256_words7_kernel<1, 0>;
+                    : c->tune_words_variant == 12 ? clt256_words7_kernel<1, 3>
+                    : c->tune_words_variant == 7 ? clt256_words7_kernel<1, 0> : clt256_words7_kernel<1, 4>;   // 0 and 14
         BBB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V7_SMEM));
         kern<<<blocks, 2 * CLT256V2_B, CLT256V7_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
         c->last_kernel = "clt256_words7";
