@@ -101,11 +101,20 @@ __device__ __forceinline__ void transpose32_fast(uint32_t (&a)[32])
 
 // The 32x32 transpose in two halves that commute: the three sub-byte stages on all 32 rows (here), and the two
 // byte-granular stages, which only mix rows k, k+8, k+16, k+24 (byte4x4_transpose on those four).
+template <bool WITH_STAGE1 = true>
 __device__ __forceinline__ void transpose32_bit_stages(uint32_t (&a)[32])
 {
     transpose_bits_stage<4, 0x0F0F0F0Fu, false>(a);
     transpose_bits_stage<2, 0x33333333u, false>(a);
-    transpose_bits_stage<1, 0x55555555u, false>(a);
+    if (WITH_STAGE1) transpose_bits_stage<1, 0x55555555u, false>(a);
+}
+
+// the last sub-byte stage on one pair of rows (k even, k + 1)
+__device__ __forceinline__ void bit_stage1_pair(uint32_t &x, uint32_t &y)
+{
+    const uint32_t a = bit_select<0x55555555u>(x, y << 1), b = bit_select<0x55555555u>(x >> 1, y);
+    x = a;
+    y = b;
 }
 
 __device__ __forceinline__ void byte4x4_transpose(uint32_t &r0, uint32_t &r1, uint32_t &r2, uint32_t &r3)

@@ -240,19 +240,23 @@ int bbb_clt_spec_blocks_per_sm(const bbb_ctx *c, int kind)
 
 // CTAs of one wave of a straight-line launch.  The raw-word kernel (clt256_words7_kernel) is the exception to "fill
 // every SM": each CTA keeps 4096 streams open and a stream's 128-byte line stays in L2 for four clocks, so the open
-// lines of 148 CTAs (78 MB) no longer fit beside each other and leave as single sectors; 128 CTAs (2^19 streams,
-// 64 MB) run the same kernel 1.27 times faster (2859 against 2255 GB/s, profiles/r2_probe_words7.txt): the largest
-// power of two that uses at least 3/4 of the SMs (a power-of-two stream count also leaves 2^k-step calls without a
-// ragged tail), else 7/8 of them.
+// lines of 148 CTAs (78 MB) no longer fit beside each other and leave as single sectors.  The best count moves down
+// as the per-SM rate goes up: 128 CTAs while the compute warps did the whole transpose (2859 against 2255 GB/s at
+// 148), 112 = three quarters of the SMs (rounded up to a multiple of 8) since the drain warps do two of its five
+// stages (3200 GB/s on two boxes; 128: 2810-3040, 104: 2980, 120: 2990; profiles/r2_probe_words7.txt).
 uint32_t bbb_clt_spec_wave_blocks(const bbb_ctx *c, int kind)
 {
     const uint32_t sms = (uint32_t)c->sm_count;
     const bool words7 = kind == 2 && c->tune_spec_variant != 1 && !c->tune_words_b192 &&
                         (c->tune_words_variant == 0 || c->tune_words_variant >= 7);
     if (!words7) return sms * (uint32_t)bbb_clt_spec_blocks_per_sm(c, kind);
-    uint32_t p2 = 1;
-    while (p2 * 2 <= sms) p2 *= 2;
-    return p2 * 4 >= sms * 3 ? p2 : sms * 7 / 8;
+    if (c->tune_words_variant == 7 || c->tune_words_variant == 8) {      // the whole transpose on the compute warps
+        uint32_t p2 = 1;
+        while (p2 * 2 <= sms) p2 *= 2;
+        return p2 * 4 >= sms * 3 ? p2 : sms * 7 / 8;
+    }
+    const uint32_t w = ((sms * 3 + 3) / 4 + 7) & ~7u;
+    return w < sms ? w : sms;
 }
 
 // Streams one CTA carries, and whether the loaded recurrence has a specialised kernel.
@@ -1136,7 +1140,7 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8])
 #define CLT256V2_W_END                                                                                               \
         }                                                                                                            \
         if (W7_BYTES) {      /* sub-byte stages here; column 4*jl + c holds row jl + 8c for the drain's byte stages */ \
-            transpose32_bit_stages(tw);                                                                              \
+            transpose32_bit_stages<!W7_STAGE1_DRAIN>(tw);                                                            \
             uint32_t tp[32];                                                                                         \
             _Pragma("unroll") for (int cc = 0; cc < 32; cc++) tp[cc] = tw[(cc >> 2) + 8 * (cc & 3)];                 \
             tmem_st32(taddr + b_ * 256u + w_ * 32u, tp);                                                             \
@@ -1159,7 +1163,8 @@ clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
 {
     constexpr bool W7_SPLIT = SPLIT == 1;
     constexpr bool W7_STRAIGHT = SPLIT == 3;      // knob words_variant = 12
-    constexpr bool W7_BYTES = SPLIT == 4;         // the byte-granular transpose stages run on the drain warps
+    constexpr bool W7_BYTES = SPLIT == 4 || SPLIT == 5;   // the byte-granular transpose stages run on the drain warps
+    constexpr bool W7_STAGE1_DRAIN = SPLIT == 5;          // ... and the last sub-byte stage (rows k, k+1) as well
     constexpr bool W7_FMA_SHR = SPLIT == 2;       // knob words_variant = 11: right shifts of the transposes on the FMA pipe
     extern __shared__ uint4 smem4[];
     const uint32_t ctrl = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
@@ -1234,6 +1239,10 @@ clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
                 if (W7_BYTES) {
 #pragma unroll
                     for (uint32_t w = 0; w < 8u; w++) {
+                        if (W7_STAGE1_DRAIN) {
+#pragma unroll
+                            for (uint32_t cq = 0; cq < 4u; cq++) bit_stage1_pair(v[w][cq], v[w][4 + cq]);
+                        }
                         byte4x4_transpose(v[w][0], v[w][1], v[w][2], v[w][3]);
                         byte4x4_transpose(v[w][4], v[w][5], v[w][6], v[w][7]);
                     }
@@ -1703,7 +1712,8 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
                     : c->tune_words_variant == 10 ? clt256_words7_kernel<1, 1>
                     : c->tune_words_variant == 11 ? clt256_words7_kernel<1, 2>
                     : c->tune_words_variant == 12 ? clt256_words7_kernel<1, 3>
-                    : c->tune_words_variant == 7 ? clt256_words7_kernel<1, 0> : clt256_words7_kernel<1, 4>;   // 0 and 14
+                    : c->tune_words_variant == 7 ? clt256_words7_kernel<1, 0>
+                    : c->tune_words_variant == 14 ? clt256_words7_kernel<1, 4> : clt256_words7_kernel<1, 5>;   // 0 and 15
         BBB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V7_SMEM));
         kern<<<blocks, 2 * CLT256V2_B, CLT256V7_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
         c->last_kernel = "clt256_words7";
