@@ -557,8 +557,8 @@ def run_secondary(args, ctx, rank, world, local_rank):
             line["roofline"] = {"bound": "hbm", "kernel": ctx.last_kernel, "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
                                 "frac": ach / hbm_peak, "traffic": None,
                                 "traffic_note": "ncu --set full of clt256_words7_kernel at 2^27 steps (profiles/r2_words7_ncu_full.txt): "
-                                                "4.226 GB written + 0.017 GB read for 4.295 GB of output = 0.99x the algorithmic bytes "
-                                                "(kernel alone 1.39 ms = 3.09 TB/s; the call adds the seeding kernel); not re-measured at this size",
+                                                "4.214 GB written + 0.017 GB read for 4.295 GB of output = 0.99x the algorithmic bytes "
+                                                "(kernel alone 1.30 ms = 3.30 TB/s; the call adds the seeding kernel); not re-measured at this size",
                                 "note": "algorithmic bytes = 32 B written per LUTOPT step (the 256-bit state, rng.py:27); "
                                         "peak = measured copy bandwidth (MEASURED_PEAKS.json), per GPU"}
         if w == "clt_stream":
