@@ -13,6 +13,16 @@
 //     generator interleaves with the next clock's instructions; samples outside
 //     96 <= popcount < 160 (|g| >= 32, about 6e-5 of them) take a rare atomic slow path into a
 //     257-bin CTA histogram.  No barrier inside the clock loop: a thread touches only its own words.
+//
+// Kernels in this file (PRODUCT = what the default build launches; the others stay reachable through tuning knobs so
+// that the GPU tests keep them bit-exact and DESIGN.md's "measured and rejected" numbers can be reproduced):
+//   clt256_hist2_kernel   PRODUCT  fused generate + histogram, one pass per clock (clt256_v2_gen.inc)
+//   clt256_hist_kernel    knob clt_spec_variant = 1: the round-1 two-pass kernel (clt256_gen.inc, layout above)
+//   clt256_s8v2_kernel    PRODUCT  int8 / int16 sample streams;  clt256_s8_kernel: two-pass predecessor
+//   clt256_dec_kernel     PRODUCT  one sample per bit period (slicer loop)
+//   clt256_words7_kernel  PRODUCT  raw URNG words, stage in tensor memory, producer / consumer warps
+//   clt256_words_kernel, _words2 ... _words6, _words8, _words9: earlier and alternative raw-word kernels
+//                         (knobs clt_spec_variant = 1, words_variant = 2 ... 13, words_b192)
 #include "bbb_internal.h"
 #include "clt_common.cuh"
 
