@@ -21,8 +21,8 @@
 //   clt256_s8v2_kernel    PRODUCT  int8 / int16 sample streams;  clt256_s8_kernel: two-pass predecessor
 //   clt256_dec_kernel     PRODUCT  one sample per bit period (slicer loop)
 //   clt256_words7_kernel  PRODUCT  raw URNG words, stage in tensor memory, producer / consumer warps
-//   clt256_words_kernel, _words2 ... _words6, _words8, _words9: earlier and alternative raw-word kernels
-//                         (knobs clt_spec_variant = 1, words_variant = 2 ... 13, words_b192)
+//   clt256_words_kernel, _words2 ... _words6, _words8 ... _words10: earlier and alternative raw-word kernels
+//                         (knobs clt_spec_variant = 1, words_variant = 2 ... 16, words_b192)
 #include "bbb_internal.h"
 #include "clt_common.cuh"
 
@@ -1301,6 +1301,101 @@ clt256_words7_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L
     __syncthreads();
     if (warp == 4u) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
 }
+// ---------------------------------------------------------------------------
+// clt256_words10_kernel (knob words_variant = 16): words7 with TWO drain warps per compute warp and the register file
+// re-divided by setmaxnreg (launch: 384 threads x 168; then the compute warpgroup 248, the two drain warpgroups 128
+// each: 4 x 32 x 248 + 8 x 32 x 128 = 64 512).  Each drain warp takes two of the four 8-stream batches of a clock, so
+// the drain's dependent chains (TMEM load -> byte / bit stages -> shuffle -> store) overlap twice as well.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(3 * CLT256V2_B, 1)
+clt256_words10_kernel(const uint32_t *__restrict__ planes, uint32_t T, uint32_t L, uint32_t *__restrict__ out)
+{
+    constexpr bool W7_SPLIT = false, W7_STRAIGHT = false, W7_BYTES = true, W7_STAGE1_DRAIN = true, W7_FMA_SHR = false;
+    (void)W7_SPLIT; (void)W7_FMA_SHR;
+    extern __shared__ uint4 smem4[];
+    const uint32_t ctrl = (uint32_t)__cvta_generic_to_shared((char *)smem4 + CLT256V2_STATE_BYTES);
+    const uint32_t warp = threadIdx.x >> 5, pair = warp & 3u, lane = threadIdx.x & 31u;
+    if (warp == 4u) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(ctrl + 128u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (threadIdx.x == 0)
+        for (uint32_t i = 0; i < 16u; i++) mbar_init(ctrl + 8u * i, (i & 2u) ? 64u : 32u);   // full: 32 arrivals, empty: 64
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tbase = *(const volatile uint32_t *)((const char *)smem4 + CLT256V2_STATE_BYTES + 128);
+    const uint32_t taddr = tbase + ((pair * 32u) << 16);
+    const uint32_t bar_full = ctrl + pair * 32u, bar_empty = bar_full + 16u;
+    if (warp >= 4u) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 128;");
+        const uint32_t half = (warp >> 2) - 1u;                          // 0: batches 0, 1; 1: batches 2, 3
+        const uint32_t odd = lane & 1u;
+        uint32_t *const opa = out + (size_t)(blockIdx.x * CLT256V2_B + pair * 32u + (lane & ~1u)) * 32u * L * 8u + 4u * odd;
+        uint32_t *const opb = opa + (size_t)32u * L * 8u;
+        uint64_t pol_keep, pol_done;
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_done));
+#pragma unroll 1
+        for (uint32_t it = 0; it < L; it++) {
+            const uint32_t b = it & 1u, k = it >> 1;
+            mbar_wait(bar_full + 8u * b, k & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+            for (uint32_t jb = half * 16u; jb < half * 16u + 16u; jb += 8u) {
+                uint32_t v[8][8];
+#pragma unroll
+                for (uint32_t w = 0; w < 8u; w++) tmem_ld8(taddr + b * 256u + w * 32u + jb, v[w]);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (uint32_t w = 0; w < 8u; w++) {
+#pragma unroll
+                    for (uint32_t cq = 0; cq < 4u; cq++) bit_stage1_pair(v[w][cq], v[w][4 + cq]);
+                    byte4x4_transpose(v[w][0], v[w][1], v[w][2], v[w][3]);
+                    byte4x4_transpose(v[w][4], v[w][5], v[w][6], v[w][7]);
+                }
+#pragma unroll
+                for (uint32_t jj = 0; jj < 8u; jj++) {
+                    uint32_t keep[4], got[4];
+#pragma unroll
+                    for (uint32_t i = 0; i < 4u; i++) {
+                        keep[i] = odd ? v[4 + i][jj] : v[i][jj];
+                        got[i] = __shfl_xor_sync(0xffffffffu, odd ? v[i][jj] : v[4 + i][jj], 1);
+                    }
+                    const uint32_t sj = (jb >> 2) + (jj >> 2) + 8u * (jj & 3u);
+                    const uint32_t sec = sj * L + it;
+                    const size_t off = (size_t)sec * 8u;
+                    const uint64_t pol = (sec & 3u) == 3u ? pol_done : pol_keep;
+                    st_policy((uint4 *)(opa + off), odd ? make_uint4(got[0], got[1], got[2], got[3])
+                                                        : make_uint4(keep[0], keep[1], keep[2], keep[3]), pol);
+                    st_policy((uint4 *)(opb + off), odd ? make_uint4(keep[0], keep[1], keep[2], keep[3])
+                                                        : make_uint4(got[0], got[1], got[2], got[3]), pol);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(bar_empty + 8u * b);
+        }
+    } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 248;");
+        const uint32_t tid = threadIdx.x;
+        const uint32_t t = blockIdx.x * CLT256V2_B + tid;
+        uint32_t *const st = (uint32_t *)smem4 + tid;
+        for (uint32_t p = 0; p < CLT256V2_NSLOTS; p++) st[p * CLT256V2_B] = planes[(size_t)CLT256V2_SLOT_BIT[p] * T + t];
+#define CLT256V2_SECTION_RESIDENT_DECL
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_RESIDENT_DECL
+
+#pragma unroll 1
+        for (uint32_t it = 0; it < L; it++) {
+#define CLT256V2_SECTION_W_BODY
+#include "clt256_v2_gen.inc"
+#undef CLT256V2_SECTION_W_BODY
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 4u) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
+}
 #pragma pop_macro("CLT256V2_W_END")
 #pragma pop_macro("CLT256V2_W_EMIT")
 #pragma pop_macro("CLT256V2_W_BEGIN")
@@ -1687,6 +1782,10 @@ int bbb_clt_spec_stream_launch(bbb_ctx *c, int kind, uint32_t blocks, uint32_t L
         clt256_s8_kernel<<<blocks, CLT256_B, CLT256S8_SMEM, c->stream>>>(planes, blocks * CLT256_B, L, (int8_t *)out,
                                                                              (int32_t)noise_var);
         c->last_kernel = "clt256_s16";
+    } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 16) {
+        BBB_CUDA(c, cudaFuncSetAttribute(clt256_words10_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V7_SMEM));
+        clt256_words10_kernel<<<blocks, 3 * CLT256V2_B, CLT256V7_SMEM, c->stream>>>(planes, blocks * CLT256V2_B, L, (uint32_t *)out);
+        c->last_kernel = "clt256_words10";
     } else if (c->tune_spec_variant != 1 && c->tune_words_variant == 13) {
         static_assert(CLT256V9_SMEM <= 227 * 1024, "shared memory budget");
         BBB_CUDA(c, cudaFuncSetAttribute(clt256_words9_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CLT256V9_SMEM));

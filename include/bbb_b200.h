@@ -96,7 +96,7 @@ uint32_t bbb_last_rounds(const bbb_ctx *ctx);
  *   shared-memory taps for every n; 2 warp per candidate, one clock per pass), "hunt_pow_k" (K: 8 or 4),
  *   "hunt_cpw" (candidates per warp pass of the one-clock warp kernel: 32 or 16),
  *   "stream_chunk_bytes", "host_copy_threads" (host-buffer stream calls),
- *   "words_variant" (raw-word stream kernel: 0 default clt256_words7; 2 clt256_words2; 4 ... 13 the
+ *   "words_variant" (raw-word stream kernel: 0 default clt256_words7; 2 clt256_words2; 4 ... 16 the
  *   measured alternatives of DESIGN.md 4.1), "words_b192" (0/1), "seed_single" (0/1: never the four-groups-per-warp seeding kernel). */
 int  bbb_set_tuning(bbb_ctx *ctx, const char *key, int64_t value);
 /* Region timer: CUDA events on the ctx's stream around any number of calls.

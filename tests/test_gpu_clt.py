@@ -272,7 +272,7 @@ def test_decimated_stream_equals_full_stream_large(ctx):
     assert bool(torch.equal(a, b[6::8]))
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16])
 @pytest.mark.parametrize("blocks,min_steps,count,first", [(1, 8, 6144 * 9 + 5, 0), (2, 8, 2 * 6144 * 11 + 3, (1 << 35) + 1)])
 def test_spec256_word_stream_matches_oracle(ctx, orc, blocks, min_steps, count, first, variant):
     """raw URNG words: two-pass clt256_words (1), one-pass clt256_words2 (2), the 192-thread experiment
@@ -280,7 +280,8 @@ def test_spec256_word_stream_matches_oracle(ctx, orc, blocks, min_steps, count, 
     line-completing evict_first stores; 9: clt256_words8, un-slicing on the drain warps;
     10: words7 with the transposes split between compute and drain warps; 11: words7 with the right shifts of the
     transposes as multiply-high on the FMA pipe; 12: the eight transposes straight-line; 13: clt256_words9, three staged clocks drained in pairs;
-    14: words7 with the byte-granular transpose stages on the drain warps (the default), 15: and the last sub-byte stage), each + the data-driven tail, == oracle"""
+    14: words7 with the byte-granular transpose stages on the drain warps (the default), 15: and the last sub-byte stage;
+    16: clt256_words10, two drain warps per compute warp with setmaxnreg), each + the data-driven tail, == oracle"""
     ctx.lutopt_load_shipped(256)
     ctx.set_tuning("clt_spec_variant", 1 if variant == 1 else 2)
     ctx.set_tuning("words_b192", 1 if variant == 3 else 0)
@@ -289,7 +290,7 @@ def test_spec256_word_stream_matches_oracle(ctx, orc, blocks, min_steps, count, 
     ctx.set_tuning("clt_spec_max_blocks", blocks)
     try:
         got = ctx.lutopt_stream(1, first, count)
-        assert ctx.last_kernel in ("generic", ("clt256_words", "clt256_words2", "clt256_words3", "clt256_words4", "clt256_words5", "clt256_words6", "clt256_words7", "clt256_words7", "clt256_words8", "clt256_words7", "clt256_words7", "clt256_words7", "clt256_words9", "clt256_words7", "clt256_words7")[variant - 1])
+        assert ctx.last_kernel in ("generic", ("clt256_words", "clt256_words2", "clt256_words3", "clt256_words4", "clt256_words5", "clt256_words6", "clt256_words7", "clt256_words7", "clt256_words8", "clt256_words7", "clt256_words7", "clt256_words7", "clt256_words9", "clt256_words7", "clt256_words7", "clt256_words10")[variant - 1])
         ref = orc.clt_run(recurrences.packed(256), 1, first, count, model=1, want=("words",))["words"]
         assert np.array_equal(got.reshape(-1), ref)
     finally:
