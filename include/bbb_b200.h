@@ -90,7 +90,8 @@ uint64_t bbb_last_d2h_bytes(const bbb_ctx *ctx);
 /* Kernel rounds the last bbb_prbs_detect needed (1 = every chunk's start state was right). */
 uint32_t bbb_last_rounds(const bbb_ctx *ctx);
 /* Tuning knobs, for tests and experiments (results never depend on them):
- *   "clt_no_spec" (0/1), "clt_spec_min_steps", "clt_spec_max_blocks",
+ *   "clt_no_spec" (0/1), "clt_spec_variant" (1: the round-1 two-pass n256 kernels, 2: one-pass), "clt_spec_min_steps",
+ *   "clt_spec_max_blocks", "dec_full_stream" (0/1: decimated samples by full stream + pick), "slicer_chunk_bits",
  *   "prbs_chunk_words", "prbs_stream_reps", "hunt_batch", "hunt_slow_check" (0/1),
  *   "hunt_smem_taps" (0 auto = warp per candidate, K clocks per pass; 1 thread-per-candidate kernel with
  *   shared-memory taps for every n; 2 warp per candidate, one clock per pass), "hunt_pow_k" (K: 8 or 4),

@@ -30,6 +30,15 @@ def test_generated_plain_clock_bodies_equal_the_recurrence():
     assert res.stdout.startswith("ok")
 
 
+def test_tuning_keys_in_the_header_are_the_ones_the_library_accepts():
+    import re
+    h = open(os.path.join(ROOT, "include", "bbb_b200.h")).read()
+    a = open(os.path.join(ROOT, "basebandboard_b200", "csrc", "api.cu")).read()
+    doc = set(re.findall(r'"([a-z0-9_]+)"', h[h.index("Tuning knobs"):h.index("int  bbb_set_tuning")]))
+    impl = set(re.findall(r'strcmp\(key, "([a-z0-9_]+)"\)', a))
+    assert doc == impl, (sorted(doc - impl), sorted(impl - doc))
+
+
 def test_bench_reference_arm_prints_the_contract_line():
     res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1",
                           "--warmup", "1", "--ref-step-seconds", "0.3", "--cpu-seconds", "0.5"],
